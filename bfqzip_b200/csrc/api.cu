@@ -1,0 +1,273 @@
+// api.cu -- the extern "C" boundary (include/bfq_gpu.h): argument checks, host<->device
+// staging, stage orchestration.  All real work is in the CUDA kernels of the other files.
+#include "common.cuh"
+#include <algorithm>
+
+namespace bfq {
+
+void byte_histogram(bfq_ctx *c, const uint8_t *d_data, uint64_t n, uint64_t hist_out[256]);
+
+static void begin_call(bfq_ctx *c)
+{
+    if (!c) BFQ_FAIL(BFQ_EINVAL, "null context");
+    BFQ_CUDA(cudaSetDevice(c->device));
+    c->arena.release(Arena::Mark{0, 0});
+    c->has_last = false;
+}
+
+// min / max read length from device offsets (also rejects non-monotone offsets)
+__global__ void __launch_bounds__(256)
+len_range_kernel(const uint64_t *__restrict__ off, uint64_t nreads, unsigned long long *__restrict__ out /*[min,max,bad]*/)
+{
+    unsigned long long mn = ~0ull, mx = 0, bad = 0;
+    for (uint64_t g = (uint64_t)blockIdx.x * 256 + threadIdx.x; g < nreads; g += (uint64_t)gridDim.x * 256) {
+        unsigned long long a = off[g], b = off[g + 1];
+        if (b < a) { bad = 1; continue; }
+        mn = min(mn, b - a);
+        mx = max(mx, b - a);
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        bad |= __shfl_xor_sync(0xffffffffu, bad, o);
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(&out[0], mn); atomicMax(&out[1], mx); if (bad) atomicOr(&out[2], 1ull); }
+}
+
+static void check_reads_dev(bfq_ctx *c, const uint64_t *d_off, uint64_t nreads, uint64_t total_bases,
+                            uint64_t *min_len, uint64_t *max_len)
+{
+    unsigned long long *d = (unsigned long long *)((char *)c->d_small + 3072);
+    unsigned long long init[4] = {~0ull, 0, 0, 0};
+    memcpy((char *)c->h_small + 3072, init, sizeof init);
+    BFQ_CUDA(cudaMemcpyAsync(d, (char *)c->h_small + 3072, 32, cudaMemcpyHostToDevice, c->stream));
+    if (nreads) {
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(nreads, 256));
+        len_range_kernel<<<grid, 256, 0, c->stream>>>(d_off, nreads, d);
+        c->launches++;
+    }
+    BFQ_CUDA(cudaMemcpyAsync((char *)c->h_small + 3072, d, 32, cudaMemcpyDeviceToHost, c->stream));
+    BFQ_CUDA(cudaMemcpyAsync((char *)c->h_small + 3072 + 32, d_off + nreads, 8, cudaMemcpyDeviceToHost, c->stream));
+    BFQ_CUDA(cudaMemcpyAsync((char *)c->h_small + 3072 + 40, d_off, 8, cudaMemcpyDeviceToHost, c->stream));
+    BFQ_CUDA(cudaStreamSynchronize(c->stream));
+    const unsigned long long *h = (const unsigned long long *)((char *)c->h_small + 3072);
+    if (h[2]) BFQ_FAIL(BFQ_EINVAL, "read offsets are not non-decreasing");
+    if (h[5] != 0 || h[4] != total_bases) BFQ_FAIL(BFQ_EINVAL, "off[0] must be 0 and off[nreads] must equal the number of bases");
+    if (nreads && h[0] == 0)
+        BFQ_FAIL(BFQ_EINVAL, "empty reads are not supported: the reference drops them (external/gsufsort/lib/utils.c:229-236); remove them first");
+    *min_len = nreads ? h[0] : 0;
+    *max_len = h[1];
+}
+
+__global__ void __launch_bounds__(256)
+export_rows_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase, uint64_t n,
+                   uint64_t code2byte, uint8_t *__restrict__ qs_out, uint8_t *__restrict__ ob_out)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t *L = lines + (i >> 5) * 64;
+    const uint32_t *H = reinterpret_cast<const uint32_t *>(L);
+    const uint32_t r = (uint32_t)(i & 31);
+    const uint32_t c = ((H[5] >> r) & 1u) | (((H[6] >> r) & 1u) << 1) | (((H[7] >> r) & 1u) << 2);
+    const uint8_t q = L[32 + r];
+    qs_out[i] = q & 0x7F;
+    ob_out[i] = (q & 0x80) ? obase[i] : (uint8_t)(code2byte >> (8 * c));
+}
+
+static void remember(bfq_ctx *c, const SmoothResult &S)
+{
+    c->last_lines = S.lines; c->last_obase = S.obase; c->last_n = S.n;
+    memcpy(c->last_code2byte, S.alpha.code2byte, 8);
+    c->has_last = true;
+}
+
+// fused device pipeline; all pointers device.  Returns through stats.
+static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                         uint64_t nreads, uint64_t total_bases, const bfq_params *P, uint8_t *d_bwt,
+                         uint8_t *d_qs, uint8_t *d_lcp, uint8_t *d_out_bases, uint8_t *d_out_quals,
+                         bfq_stats *stats)
+{
+    uint64_t mn, mx;
+    check_reads_dev(c, d_off, nreads, total_bases, &mn, &mx);
+    const uint64_t N = total_bases + nreads;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (N == 0) return;
+    if (!d_bwt) d_bwt = arena_alloc<uint8_t>(c, N + 64);
+    if (!d_qs) d_qs = arena_alloc<uint8_t>(c, N + 64);
+    if (!d_lcp) d_lcp = arena_alloc<uint8_t>(c, N + 64);
+    {
+        Arena::Mark mk = c->arena.mark();
+        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, P->eos_byte, d_bwt, d_qs, d_lcp, nullptr);
+        c->arena.release(mk);        // sort scratch is dead (stream-ordered) once the gather is queued
+    }
+    SmoothResult S;
+    smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats);
+    if (S.nreads != nreads) BFQ_FAIL(BFQ_ECUDA, "internal error: %llu end-markers for %llu reads", (unsigned long long)S.nreads, (unsigned long long)nreads);
+    if (mx <= (uint64_t)P->max_len) {
+        rebuild_dev(c, S, P, d_off, d_out_bases, d_out_quals, nullptr, nullptr);
+    } else {
+        // reads longer than -l are truncated by the reference (decode.cpp:605): general path
+        uint64_t *d_oo = arena_alloc<uint64_t>(c, nreads + 1);
+        rebuild_dev(c, S, P, nullptr, d_out_bases, d_out_quals, d_oo, nullptr);
+    }
+    BFQ_CUDA(cudaStreamSynchronize(c->stream));
+    remember(c, S);
+}
+
+} // namespace bfq
+
+using namespace bfq;
+
+#define API_BEGIN try { begin_call(ctx);
+#define API_END   return BFQ_OK; } catch (bfq::Error &e__) { if (ctx) cudaStreamSynchronize(ctx->stream); cudaGetLastError(); return e__.code; } \
+                  catch (std::exception &ex__) { bfq::set_error("exception: %s", ex__.what()); return BFQ_ENOMEM; }
+
+static uint64_t host_check_off(const uint64_t *off, uint64_t nreads)
+{
+    if (off[0] != 0) BFQ_FAIL(BFQ_EINVAL, "off[0] must be 0");
+    for (uint64_t g = 0; g < nreads; g++) {
+        if (off[g + 1] < off[g]) BFQ_FAIL(BFQ_EINVAL, "read offsets are not non-decreasing (read %llu)", (unsigned long long)g);
+        if (off[g + 1] == off[g])
+            BFQ_FAIL(BFQ_EINVAL, "read %llu is empty: the reference drops empty reads (external/gsufsort/lib/utils.c:229-236); remove them first", (unsigned long long)g);
+    }
+    return off[nreads];
+}
+
+template <typename T> static T *to_device(bfq_ctx *c, const T *h, uint64_t count, uint64_t pad = 16)
+{
+    T *d = arena_alloc<T>(c, count + pad);
+    if (count) BFQ_CUDA(cudaMemcpyAsync(d, h, count * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+    return d;
+}
+
+extern "C" {
+
+int bfq_build_ebwt(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const uint64_t *off,
+                   uint64_t nreads, uint8_t eos_byte, uint8_t *bwt, uint8_t *qs, uint8_t *lcp)
+{
+    API_BEGIN
+    if (!off || !bwt || !qs || !lcp || (nreads && (!bases || !quals))) BFQ_FAIL(BFQ_EINVAL, "bfq_build_ebwt: null pointer");
+    const uint64_t total = host_check_off(off, nreads), N = total + nreads;
+    if (N == 0) return BFQ_OK;
+    uint8_t *d_b = to_device(ctx, bases, total), *d_q = to_device(ctx, quals, total);
+    uint64_t *d_o = to_device(ctx, off, nreads + 1);
+    uint8_t *d_bwt = arena_alloc<uint8_t>(ctx, N + 64), *d_qs = arena_alloc<uint8_t>(ctx, N + 64), *d_lcp = arena_alloc<uint8_t>(ctx, N + 64);
+    build_ebwt_dev(ctx, d_b, d_q, d_o, nreads, total, eos_byte, d_bwt, d_qs, d_lcp, nullptr);
+    BFQ_CUDA(cudaMemcpyAsync(bwt, d_bwt, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(qs, d_qs, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(lcp, d_lcp, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int bfq_smooth_rebuild(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, const uint8_t *lcp, uint64_t n,
+                       const bfq_params *params, uint8_t *out_bases, uint8_t *out_quals, uint64_t *out_off,
+                       uint64_t off_capacity, bfq_stats *stats)
+{
+    API_BEGIN
+    if (!params || !out_off || (n && (!bwt || !qs || !lcp || !out_bases || !out_quals))) BFQ_FAIL(BFQ_EINVAL, "bfq_smooth_rebuild: null pointer");
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (n == 0) { if (off_capacity < 1) BFQ_FAIL(BFQ_ECAPACITY, "out_off too small"); out_off[0] = 0; return BFQ_OK; }
+    uint8_t *d_bwt = to_device(ctx, bwt, n, 64), *d_qs = to_device(ctx, qs, n, 64), *d_lcp = to_device(ctx, lcp, n, 64);
+    SmoothResult S;
+    smooth_dev(ctx, d_bwt, d_qs, d_lcp, n, params, &S, stats);
+    if (S.nreads + 1 > off_capacity) BFQ_FAIL(BFQ_ECAPACITY, "out_off holds %llu entries, %llu needed", (unsigned long long)off_capacity, (unsigned long long)(S.nreads + 1));
+    uint8_t *d_ob = arena_alloc<uint8_t>(ctx, n + 64), *d_oq = arena_alloc<uint8_t>(ctx, n + 64);
+    uint64_t *d_oo = arena_alloc<uint64_t>(ctx, S.nreads + 1);
+    uint64_t total = 0;
+    rebuild_dev(ctx, S, params, nullptr, d_ob, d_oq, d_oo, &total);
+    if (total) {
+        BFQ_CUDA(cudaMemcpyAsync(out_bases, d_ob, total, cudaMemcpyDeviceToHost, ctx->stream));
+        BFQ_CUDA(cudaMemcpyAsync(out_quals, d_oq, total, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    BFQ_CUDA(cudaMemcpyAsync(out_off, d_oo, (S.nreads + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    remember(ctx, S);
+    API_END
+}
+
+int bfq_pipeline(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const uint64_t *off, uint64_t nreads,
+                 const bfq_params *params, uint8_t *bwt, uint8_t *qs, uint8_t *lcp, uint8_t *out_bases,
+                 uint8_t *out_quals, bfq_stats *stats)
+{
+    API_BEGIN
+    if (!params || !off || (nreads && (!bases || !quals || !out_bases || !out_quals))) BFQ_FAIL(BFQ_EINVAL, "bfq_pipeline: null pointer");
+    const uint64_t total = host_check_off(off, nreads), N = total + nreads;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (N == 0) return BFQ_OK;
+    uint8_t *d_b = to_device(ctx, bases, total), *d_q = to_device(ctx, quals, total);
+    uint64_t *d_o = to_device(ctx, off, nreads + 1);
+    uint8_t *d_bwt = arena_alloc<uint8_t>(ctx, N + 64), *d_qs = arena_alloc<uint8_t>(ctx, N + 64), *d_lcp = arena_alloc<uint8_t>(ctx, N + 64);
+    uint8_t *d_ob = arena_alloc<uint8_t>(ctx, total + 64), *d_oq = arena_alloc<uint8_t>(ctx, total + 64);
+    pipeline_dev(ctx, d_b, d_q, d_o, nreads, total, params, d_bwt, d_qs, d_lcp, d_ob, d_oq, stats);
+    if (bwt) BFQ_CUDA(cudaMemcpyAsync(bwt, d_bwt, N, cudaMemcpyDeviceToHost, ctx->stream));
+    if (qs) BFQ_CUDA(cudaMemcpyAsync(qs, d_qs, N, cudaMemcpyDeviceToHost, ctx->stream));
+    if (lcp) BFQ_CUDA(cudaMemcpyAsync(lcp, d_lcp, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(out_bases, d_ob, total, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(out_quals, d_oq, total, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                     uint64_t nreads, uint64_t total_bases, const bfq_params *params, uint8_t *d_bwt,
+                     uint8_t *d_qs, uint8_t *d_lcp, uint8_t *d_out_bases, uint8_t *d_out_quals, bfq_stats *stats)
+{
+    API_BEGIN
+    if (!params || !d_off || (nreads && (!d_bases || !d_quals || !d_out_bases || !d_out_quals))) BFQ_FAIL(BFQ_EINVAL, "bfq_pipeline_dev: null pointer");
+    pipeline_dev(ctx, d_bases, d_quals, d_off, nreads, total_bases, params, d_bwt, d_qs, d_lcp, d_out_bases, d_out_quals, stats);
+    API_END
+}
+
+int bfq_export_rows(bfq_ctx *ctx, uint8_t *qs_out, uint8_t *obwt_out)
+{
+    try {
+        if (!ctx || !qs_out || !obwt_out) BFQ_FAIL(BFQ_EINVAL, "bfq_export_rows: null pointer");
+        if (!ctx->has_last) BFQ_FAIL(BFQ_EINVAL, "bfq_export_rows: no smooth/pipeline result is held by this context");
+        BFQ_CUDA(cudaSetDevice(ctx->device));
+        const uint64_t n = ctx->last_n;
+        Arena::Mark mk = ctx->arena.mark();
+        uint8_t *dq = arena_alloc<uint8_t>(ctx, n + 64), *db = arena_alloc<uint8_t>(ctx, n + 64);
+        uint64_t c2b = 0;
+        for (int k = 0; k < 8; k++) c2b |= (uint64_t)ctx->last_code2byte[k] << (8 * k);
+        export_rows_kernel<<<div_up(n, 256), 256, 0, ctx->stream>>>(ctx->last_lines, ctx->last_obase, n, c2b, dq, db);
+        ctx->launches++;
+        BFQ_CUDA(cudaMemcpyAsync(qs_out, dq, n, cudaMemcpyDeviceToHost, ctx->stream));
+        BFQ_CUDA(cudaMemcpyAsync(obwt_out, db, n, cudaMemcpyDeviceToHost, ctx->stream));
+        BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+        ctx->arena.release(mk);
+        return BFQ_OK;
+    } catch (bfq::Error &e) { return e.code; }
+}
+
+int bfq_debug_sort_pairs(bfq_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t n, int bits)
+{
+    API_BEGIN
+    if (!keys || !vals) BFQ_FAIL(BFQ_EINVAL, "null pointer");
+    if (bits < 0 || bits > 64) BFQ_FAIL(BFQ_EINVAL, "bits must be 0..64");
+    uint64_t *ka = to_device(ctx, keys, n), *kb = arena_alloc<uint64_t>(ctx, n + 16);
+    uint32_t *va = to_device(ctx, vals, n), *vb = arena_alloc<uint32_t>(ctx, n + 16);
+    int flip = radix_sort_pairs64(ctx, ka, kb, va, vb, n, bits);
+    BFQ_CUDA(cudaMemcpyAsync(keys, flip ? kb : ka, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(vals, flip ? vb : va, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int bfq_debug_suffix_array(bfq_ctx *ctx, const uint8_t *bases, const uint64_t *off, uint64_t nreads, uint32_t *sa)
+{
+    API_BEGIN
+    if (!off || !sa || (nreads && !bases)) BFQ_FAIL(BFQ_EINVAL, "null pointer");
+    const uint64_t total = host_check_off(off, nreads), N = total + nreads;
+    if (N == 0) return BFQ_OK;
+    uint8_t *d_b = to_device(ctx, bases, total);
+    uint64_t *d_o = to_device(ctx, off, nreads + 1);
+    uint32_t *d_sa = arena_alloc<uint32_t>(ctx, N + 16);
+    build_ebwt_dev(ctx, d_b, d_b, d_o, nreads, total, '#', nullptr, nullptr, nullptr, d_sa);
+    BFQ_CUDA(cudaMemcpyAsync(sa, d_sa, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+} // extern "C"

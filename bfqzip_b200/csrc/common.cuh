@@ -1,0 +1,155 @@
+// common.cuh -- context, device arena, error plumbing and launch accounting shared by all
+// translation units of libbfqgpu.  sm_100a only; no CPU fallback anywhere in this library.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <map>
+#include "../../include/bfq_gpu.h"
+
+#ifndef BFQ_M
+#define BFQ_M 2
+#endif
+#ifndef BFQ_B
+#define BFQ_B 0
+#endif
+
+namespace bfq {
+
+void set_error(const char *fmt, ...);
+
+struct Error { int code; };   // thrown inside the library, caught at the C ABI
+
+#define BFQ_CUDA(call)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (call);                                                        \
+        if (e__ != cudaSuccess) {                                                        \
+            bfq::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call,                 \
+                           cudaGetErrorString(e__));                                     \
+            throw bfq::Error{e__ == cudaErrorMemoryAllocation ? BFQ_ENOMEM : BFQ_ECUDA}; \
+        }                                                                                \
+    } while (0)
+
+#define BFQ_FAIL(code, ...)          \
+    do {                             \
+        bfq::set_error(__VA_ARGS__); \
+        throw bfq::Error{code};      \
+    } while (0)
+
+// ---------------------------------------------------------------- profiling classes
+enum ProfClass {
+    PC_RADIX_PASS = 0, PC_RADIX_HIST, PC_PACK, PC_KEYS, PC_REGROUP, PC_GATHER, PC_HIST, PC_RANK,
+    PC_CLUSTER, PC_CLUSTER_LONG, PC_RULE11, PC_WALK, PC_ASSEMBLE, PC_COUNT
+};
+static const char *const kProfNames[PC_COUNT] = {
+    "radix_pass", "radix_hist", "pack", "keys", "regroup", "gather", "hist", "rank",
+    "cluster", "cluster_long", "rule11", "walk", "assemble"};
+
+struct ProfEntry {
+    double ms = 0; uint64_t launches = 0; uint64_t bytes = 0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+};
+
+// ---------------------------------------------------------------- device arena
+// One growing cudaMalloc'd slab list with stack discipline: mark()/release(mark).
+struct Arena {
+    struct Slab { char *base; size_t size; size_t used; };
+    std::vector<Slab> slabs;
+    size_t min_slab = (size_t)256 << 20;
+    void *alloc(size_t bytes);
+    struct Mark { size_t slab; size_t used; };
+    Mark mark() const;
+    void release(Mark m);
+    void destroy();
+    size_t total() const { size_t t = 0; for (auto &s : slabs) t += s.size; return t; }
+};
+
+} // namespace bfq
+
+struct bfq_ctx {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    bfq::Arena arena;
+    // host pinned scratch for small read-backs
+    uint64_t *h_small = nullptr;      // 4 KiB pinned
+    uint64_t *d_small = nullptr;      // 4 KiB device
+    // options
+    int opt_initial_k = 0;
+    int64_t opt_long_cluster = 1024;
+    int opt_profile = 0;
+    // accounting
+    uint64_t launches = 0;
+    bfq::ProfEntry prof[bfq::PC_COUNT];
+    std::vector<cudaEvent_t> event_pool;
+    // state kept after smooth/pipeline for bfq_export_rows
+    const uint8_t *last_lines = nullptr;   // walk lines (device)
+    const uint8_t *last_obase = nullptr;   // modified-base side array (device)
+    uint64_t last_n = 0;
+    uint8_t last_code2byte[8] = {0};
+    bfq::Arena::Mark last_mark{0, 0};
+    bool has_last = false;
+};
+
+namespace bfq {
+
+// RAII profile scope: records two events around a kernel class when profiling is on,
+// always counts the launch.
+struct ProfScope {
+    bfq_ctx *c; ProfClass k; cudaEvent_t e0 = nullptr, e1 = nullptr;
+    ProfScope(bfq_ctx *ctx, ProfClass klass, uint64_t bytes, uint64_t nlaunch = 1);
+    ~ProfScope();
+};
+void prof_collect(bfq_ctx *c);   // resolves pending event pairs (after a stream sync)
+
+template <typename T> inline T *arena_alloc(bfq_ctx *c, size_t count)
+{
+    return (T *)c->arena.alloc(count * sizeof(T));
+}
+
+inline unsigned div_up(uint64_t a, uint64_t b) { return (unsigned)((a + b - 1) / b); }
+
+// ---- pipeline stages (implemented across the .cu files) -----------------------------
+struct Alphabet {
+    int nsym = 0;                 // non-EOS symbols, <= 5
+    uint8_t code2byte[8] = {0};   // code 0 = EOS byte, 1..nsym = symbols in byte order
+    uint8_t byte2code[256];       // 0xFF = not in alphabet
+    int code_N = -1;              // code of 'N' or -1
+    uint8_t acgt_mask = 0;        // bit c set when code c is one of A,C,G,T
+};
+
+struct EbwtDev {                 // device results of part A
+    uint8_t *bwt = nullptr, *qs = nullptr, *lcp = nullptr;
+    uint64_t n = 0;
+};
+
+// sufsort.cu
+void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                    uint64_t nreads, uint64_t total_bases, uint8_t eos_byte,
+                    uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out);
+// smooth.cu
+struct SmoothResult {
+    uint8_t *lines = nullptr;     // 64 B per 32 rows: u32 cnt[5], u32 plane[3], u8 q[32]
+    uint8_t *obase = nullptr;     // n bytes, valid where q&0x80
+    uint64_t n = 0, nreads = 0;
+    Alphabet alpha;
+};
+void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
+                uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats);
+// rebuild.cu
+// d_len_known: per-read lengths offsets (nreads+1, u64) or NULL.  Writes reads in input order.
+void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P,
+                 const uint64_t *d_off_known, uint8_t *d_out_bases, uint8_t *d_out_quals,
+                 uint64_t *d_out_off, uint64_t *total_out);
+// radix.cu
+// Stable LSD sort of (key,val) on key bits [0,bits).  Result ends in keys_a/vals_a when the
+// returned flag is 0, in keys_b/vals_b when 1 (ping-pong buffers, both n long).
+int radix_sort_pairs64(bfq_ctx *c, uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a,
+                       uint32_t *vals_b, uint64_t n, int bits);
+int radix_sort_pairs32(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a,
+                       uint32_t *vals_b, uint64_t n, int bits);
+
+} // namespace bfq

@@ -1,0 +1,305 @@
+// radix.cu -- stable LSD radix sort of (key, 32-bit payload) pairs, one-sweep style.
+//
+// This is the hot kernel of part A (SURVEY.md 8(a) row a3 replaces the sequential induced
+// sorting of external/gsufsort/external/gsacak.c:1648-1930 with prefix doubling over radix
+// passes).  Per pass every key and payload is read once and written once:
+//   * rs_hist_kernel    one read of the keys builds the digit histograms of ALL passes
+//                       (shared-memory histograms, warp-aggregated with __match_any_sync);
+//   * rs_onesweep_kernel per tile: warp-striped coalesced loads, match-based stable ranking,
+//                       chained-scan ("decoupled look-back") of the per-tile digit counts so no
+//                       second read is needed, shared-memory staging so that every digit's run
+//                       leaves the SM as contiguous, coalesced stores.
+// HBM-bound integer work: no tensor cores.  Algorithmic bytes per pass = 2*(sizeof(K)+4)*n.
+#include "common.cuh"
+
+namespace bfq {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_RADIX = 256;
+constexpr int RS_MAX_PASSES = 8;
+
+struct RsPasses {
+    int num;
+    int shift[RS_MAX_PASSES];
+    int bits[RS_MAX_PASSES];
+};
+
+static RsPasses plan_passes(int bits)
+{
+    RsPasses p{};
+    p.num = (bits + 7) / 8;
+    int base = p.num ? bits / p.num : 0, rem = p.num ? bits % p.num : 0, sh = 0;
+    for (int i = 0; i < p.num; i++) {
+        p.bits[i] = base + (i < rem ? 1 : 0);
+        p.shift[i] = sh;
+        sh += p.bits[i];
+    }
+    return p;
+}
+
+template <typename K> __device__ __forceinline__ uint32_t digit_of(K k, int shift, uint32_t mask)
+{
+    return (uint32_t)(k >> shift) & mask;
+}
+
+// ------------------------------------------------------------------------------ histogram
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_hist_kernel(const K *__restrict__ keys, uint64_t n, RsPasses P, uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[RS_MAX_PASSES][RS_RADIX];
+    for (int i = threadIdx.x; i < RS_MAX_PASSES * RS_RADIX; i += RS_THREADS) (&sh[0][0])[i] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+    for (uint64_t base = (uint64_t)blockIdx.x * RS_THREADS; base < n; base += stride) {
+        const uint64_t i = base + threadIdx.x;          // block-uniform trip count
+        const bool ok = i < n;
+        K k = ok ? keys[i] : (K)0;
+#pragma unroll
+        for (int p = 0; p < RS_MAX_PASSES; p++) {
+            if (p < P.num) {
+                uint32_t d = ok ? digit_of(k, P.shift[p], (1u << P.bits[p]) - 1) : 0xffffffffu;
+                // warp-aggregated: one shared atomic per distinct digit in the warp
+                uint32_t m = __match_any_sync(0xffffffffu, d);
+                if (ok && (__ffs(m) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[p][d], __popc(m));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < P.num * RS_RADIX; i += RS_THREADS) {
+        uint32_t v = (&sh[0][0])[i];
+        if (v) atomicAdd(&hist[i], v);
+    }
+}
+
+// exclusive scan of each pass's 256 counters, in place (one block per pass)
+__global__ void rs_scan_hist_kernel(uint32_t *hist)
+{
+    __shared__ uint32_t warp_tot[RS_WARPS];
+    uint32_t *h = hist + blockIdx.x * RS_RADIX;
+    int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    uint32_t v = h[t], x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_tot[w] = x;
+    __syncthreads();
+    uint32_t add = 0;
+    for (int i = 0; i < w; i++) add += warp_tot[i];
+    h[t] = x - v + add;
+}
+
+// ------------------------------------------------------------------------------ onesweep
+// status word: [flag:2][value].  flag 1 = tile aggregate, 2 = inclusive prefix.
+template <typename S> struct StatusTraits;
+template <> struct StatusTraits<uint32_t> { static constexpr int FS = 30; };
+template <> struct StatusTraits<uint64_t> { static constexpr int FS = 62; };
+
+template <typename S> __device__ __forceinline__ S ld_status(const S *p)
+{
+    return *((const volatile S *)p);
+}
+template <typename S> __device__ __forceinline__ void st_status(S *p, S v)
+{
+    *((volatile S *)p) = v;
+}
+
+template <typename K, typename S, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
+                   const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out,
+                   uint32_t n, int shift, int bits, const uint32_t *__restrict__ digit_base,
+                   S *__restrict__ status, uint32_t *__restrict__ tile_counter)
+{
+    constexpr int TILE = RS_THREADS * ITEMS;
+    constexpr int FS = StatusTraits<S>::FS;
+    constexpr S VMASK = (((S)1) << FS) - 1;
+
+    __shared__ uint32_t s_tile;
+    __shared__ uint32_t warp_cnt[RS_WARPS][RS_RADIX];
+    __shared__ uint32_t digit_start[RS_RADIX];
+    __shared__ uint32_t digit_gbase[RS_RADIX];
+    __shared__ uint32_t warp_tot[RS_WARPS];
+    __shared__ K stage[TILE];
+
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t mask = (1u << bits) - 1;
+    const uint32_t lt = (1u << lane) - 1;
+
+    if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+    for (int i = tid; i < RS_WARPS * RS_RADIX; i += RS_THREADS) (&warp_cnt[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t tile_base = tile * (uint32_t)TILE;
+    const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+
+    // ---- load keys (warp-striped: item i of lane l sits at warp_base + i*32 + l)
+    K key[ITEMS];
+    const uint32_t wbase = w * (ITEMS * 32) + lane;
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t loc = wbase + i * 32;
+        key[i] = (loc < valid) ? keys_in[tile_base + loc] : (K)~(K)0;
+    }
+    // ---- stable in-warp ranking
+    uint16_t rank[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t d = digit_of(key[i], shift, mask);
+        uint32_t m = __match_any_sync(0xffffffffu, d);
+        uint32_t prev = warp_cnt[w][d];
+        __syncwarp();
+        if ((__ffs(m) - 1) == lane) warp_cnt[w][d] = prev + __popc(m);
+        __syncwarp();
+        rank[i] = (uint16_t)(prev + __popc(m & lt));
+    }
+    __syncthreads();
+
+    // ---- per-digit totals over warps (thread d owns digit d), publish tile aggregate
+    uint32_t count;
+    {
+        uint32_t acc = 0;
+#pragma unroll
+        for (int ww = 0; ww < RS_WARPS; ww++) {
+            uint32_t t = warp_cnt[ww][tid];
+            warp_cnt[ww][tid] = acc;
+            acc += t;
+        }
+        count = acc;
+        // padding keys are all-ones: they were ranked into the top digit; do not count them
+        if ((uint32_t)tid == mask) count -= ((uint32_t)TILE - valid);
+        // (padding has digit == mask because the key is all ones)
+    }
+    S *my_status = status + (size_t)tile * RS_RADIX + tid;
+    st_status<S>(my_status, ((S)(tile == 0 ? 2 : 1) << FS) | (S)count);
+
+    // ---- exclusive scan of the 256 counts -> local start of each digit inside the tile
+    {
+        uint32_t x = count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) warp_tot[w] = x;
+        __syncthreads();
+        uint32_t add = 0;
+#pragma unroll
+        for (int i = 0; i < RS_WARPS; i++) if (i < w) add += warp_tot[i];
+        digit_start[tid] = x - count + add;
+    }
+    __syncthreads();
+
+    // ---- scatter keys into the staging buffer at their tile-local sorted position
+    uint16_t lpos[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t d = digit_of(key[i], shift, mask);
+        uint32_t p = digit_start[d] + warp_cnt[w][d] + rank[i];
+        lpos[i] = (uint16_t)p;
+        stage[p] = key[i];
+    }
+
+    // ---- chained scan: exclusive prefix of this digit over all earlier tiles
+    {
+        uint32_t excl = 0;
+        if (tile > 0) {
+            int64_t t = (int64_t)tile - 1;
+            while (true) {
+                S v = ld_status<S>(status + (size_t)t * RS_RADIX + tid);
+                uint32_t f = (uint32_t)(v >> FS);
+                if (f == 0) continue;
+                excl += (uint32_t)(v & VMASK);
+                if (f == 2) break;
+                t--;
+            }
+            st_status<S>(my_status, ((S)2 << FS) | (S)((S)excl + (S)count));
+        }
+        digit_gbase[tid] = digit_base[tid] + excl - digit_start[tid];
+    }
+    __syncthreads();
+
+    // ---- coalesced output of keys; remember each slot's global index for the payload
+    uint32_t gidx[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t slot = i * RS_THREADS + tid;
+        K k = stage[slot];
+        uint32_t d = digit_of(k, shift, mask);
+        gidx[i] = digit_gbase[d] + slot;
+        if (slot < valid) keys_out[gidx[i]] = k;
+    }
+    __syncthreads();
+
+    // ---- payload through the same permutation
+    uint32_t *stage32 = reinterpret_cast<uint32_t *>(stage);
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t loc = wbase + i * 32;
+        uint32_t v = (loc < valid) ? vals_in[tile_base + loc] : 0u;
+        stage32[lpos[i]] = v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t slot = i * RS_THREADS + tid;
+        if (slot < valid) vals_out[gidx[i]] = stage32[slot];
+    }
+}
+
+// ------------------------------------------------------------------------------ host driver
+template <typename K, int ITEMS>
+static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint32_t *vals_b,
+                            uint64_t n, int bits)
+{
+    if (n == 0 || bits <= 0) return 0;
+    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    constexpr int TILE = RS_THREADS * ITEMS;
+    RsPasses P = plan_passes(bits);
+    Arena::Mark mk = c->arena.mark();
+    const uint32_t tiles = div_up(n, TILE);
+    const bool wide = n >= ((uint64_t)1 << 30);
+    const size_t status_bytes = (size_t)tiles * RS_RADIX * (wide ? 8 : 4) + 256;
+    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
+    char *status = (char *)c->arena.alloc(status_bytes);
+    uint32_t *tile_counter = (uint32_t *)(status + (size_t)tiles * RS_RADIX * (wide ? 8 : 4));
+
+    BFQ_CUDA(cudaMemsetAsync(hist, 0, RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), c->stream));
+    {
+        ProfScope ps(c, PC_RADIX_HIST, n * sizeof(K), 2);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
+        rs_hist_kernel<K><<<grid, RS_THREADS, 0, c->stream>>>(keys_a, n, P, hist);
+        rs_scan_hist_kernel<<<P.num, RS_RADIX, 0, c->stream>>>(hist);
+    }
+    K *kin = keys_a, *kout = keys_b;
+    uint32_t *vin = vals_a, *vout = vals_b;
+    for (int p = 0; p < P.num; p++) {
+        BFQ_CUDA(cudaMemsetAsync(status, 0, status_bytes, c->stream));
+        {
+            ProfScope ps(c, PC_RADIX_PASS, 2 * n * (sizeof(K) + 4));
+            if (wide)
+                rs_onesweep_kernel<K, uint64_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
+                    kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
+                    (uint64_t *)status, tile_counter);
+            else
+                rs_onesweep_kernel<K, uint32_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
+                    kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
+                    (uint32_t *)status, tile_counter);
+        }
+        BFQ_CUDA(cudaGetLastError());
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+    // The arena memory (hist/status) is reused by later allocations only after stream order
+    // guarantees completion: everything runs on c->stream.
+    c->arena.release(mk);
+    return (P.num & 1);
+}
+
+int radix_sort_pairs64(bfq_ctx *c, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, uint64_t n, int bits)
+{
+    return radix_sort_pairs<uint64_t, 16>(c, ka, kb, va, vb, n, bits);
+}
+int radix_sort_pairs32(bfq_ctx *c, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, uint64_t n, int bits)
+{
+    return radix_sort_pairs<uint32_t, 16>(c, ka, kb, va, vb, n, bits);
+}
+
+} // namespace bfq

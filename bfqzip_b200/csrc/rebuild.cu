@@ -1,0 +1,181 @@
+// rebuild.cu -- part C on the device: every read is an independent inverse-LF walk over the
+// walk lines built by smooth.cu, emitting (output base, stored quality) backwards.
+//
+// Replaces: src_ext_mem/decode.cpp decodeBCRmultipleReverse
+// :499-686, RecoverNsymbolsReverseByVector :691-966 (one fseek+fread pair per symbol there,
+// one 64-byte line fetch here), transposeCycFile :409-496 (no analogue: reads are written in
+// place), convertFromCycFileToFastaOrFastq :968-1152 (strip, reverse).
+// Read g starts at row g (decode.cpp:578-582); at most max_len symbols are recovered
+// (decode.cpp:605); the walk stops at the end-marker (decode.cpp:890-891).
+#include "common.cuh"
+#include <algorithm>
+
+namespace bfq {
+
+struct WalkHdr { uint32_t cnt[5]; uint32_t plane[3]; };
+
+// off_known != NULL: read lengths are known (fused pipeline) -> symbols go straight to their
+// final place.  Otherwise they go to a [nreads x max_len] scratch in walk order and lens[g]
+// records how many were found; assemble_kernel reverses and compacts them.
+__global__ void __launch_bounds__(256)
+walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase, uint32_t nreads,
+            int max_len, uint64_t code2byte, const uint64_t *__restrict__ off_known,
+            uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q, uint32_t *__restrict__ lens)
+{
+    const uint32_t g = blockIdx.x * 256u + threadIdx.x;
+    if (g >= nreads) return;
+    uint64_t row = g;
+    uint64_t wpos;            // next write index
+    if (off_known) wpos = off_known[g + 1];
+    else wpos = (uint64_t)g * (uint32_t)max_len;
+    int k = 0;
+    for (; k < max_len; k++) {
+        const uint8_t *L = lines + (row >> 5) * 64;
+        const uint4 a = *reinterpret_cast<const uint4 *>(L);
+        const uint4 b = *reinterpret_cast<const uint4 *>(L + 16);
+        const uint32_t r = (uint32_t)(row & 31);
+        const uint32_t p0 = b.y, p1 = b.z, p2 = b.w;
+        const uint32_t c = ((p0 >> r) & 1u) | (((p1 >> r) & 1u) << 1) | (((p2 >> r) & 1u) << 2);
+        if (c == 0) break;                                   // end-marker: read complete
+        const uint8_t q = L[32 + r];
+        uint8_t base = (uint8_t)(code2byte >> (8 * c));
+        if (q & 0x80) base = obase[row];                     // noise-reduced row (BWT_MOD, bfq_ext.cpp:555)
+        if (off_known) { wpos--; out_b[wpos] = base; out_q[wpos] = q & 0x7F; }
+        else { out_b[wpos] = base; out_q[wpos] = q & 0x7F; wpos++; }
+        const uint32_t mm = ((c & 1) ? p0 : ~p0) & ((c & 2) ? p1 : ~p1) & ((c & 4) ? p2 : ~p2);
+        const uint32_t cnt = c == 1 ? a.x : c == 2 ? a.y : c == 3 ? a.z : c == 4 ? a.w : b.x;
+        row = (uint64_t)cnt + __popc(mm & ((1u << r) - 1u));
+    }
+    if (lens) lens[g] = (uint32_t)k;
+}
+
+// ---- exclusive scan u32 -> u64 (three small kernels; R elements, a few MB)
+__global__ void __launch_bounds__(256) scan_reduce_kernel(const uint32_t *in, uint32_t n, unsigned long long *blk)
+{
+    __shared__ unsigned long long s[8];
+    uint32_t i0 = blockIdx.x * 1024u + threadIdx.x * 4u;
+    unsigned long long v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) if (i0 + k < n) v += in[i0 + k];
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) { unsigned long long t = 0; for (int k = 0; k < 8; k++) t += s[k]; blk[blockIdx.x] = t; }
+}
+__global__ void __launch_bounds__(1024) scan_blocks_kernel(unsigned long long *blk, uint32_t nblk, unsigned long long *total)
+{
+    __shared__ unsigned long long s_warp[32];
+    __shared__ unsigned long long s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nblk; base += 1024) {
+        uint32_t i = base + tid;
+        unsigned long long v = i < nblk ? blk[i] : 0, x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) s_warp[w] = x;
+        __syncthreads();
+        unsigned long long add = 0;
+        for (int j = 0; j < w; j++) add += s_warp[j];
+        unsigned long long carry = s_carry;
+        if (i < nblk) blk[i] = carry + add + x - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + add + x;
+        __syncthreads();
+    }
+    if (tid == 0) *total = s_carry;
+}
+__global__ void __launch_bounds__(256) scan_down_kernel(const uint32_t *in, uint32_t n, const unsigned long long *blk,
+                                                       unsigned long long *out, const unsigned long long *total)
+{
+    __shared__ unsigned long long s[8];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    uint32_t i0 = blockIdx.x * 1024u + tid * 4u;
+    uint32_t v[4]; unsigned long long sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { v[k] = (i0 + k < n) ? in[i0 + k] : 0; sum += v[k]; }
+    unsigned long long x = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { unsigned long long y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) s[w] = x;
+    __syncthreads();
+    unsigned long long add = blk[blockIdx.x];
+    for (int j = 0; j < w; j++) add += s[j];
+    unsigned long long run = add + x - sum;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { if (i0 + k < n) out[i0 + k] = run; run += v[k]; }
+    if (blockIdx.x == 0 && tid == 0) out[n] = *total;
+}
+
+// one warp per read: reverse the walk-order scratch into the final position
+__global__ void __launch_bounds__(256)
+assemble_kernel(const uint8_t *__restrict__ sb, const uint8_t *__restrict__ sq, const uint32_t *__restrict__ lens,
+                const unsigned long long *__restrict__ off, uint32_t nreads, int max_len,
+                uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp0 = (blockIdx.x * 256u + threadIdx.x) >> 5, nwarps = (gridDim.x * 256u) >> 5;
+    for (uint32_t g = warp0; g < nreads; g += nwarps) {
+        const uint32_t len = lens[g];
+        const uint64_t src = (uint64_t)g * (uint32_t)max_len, dst = off[g];
+        for (uint32_t j = lane; j < len; j += 32) {
+            out_b[dst + j] = sb[src + (len - 1 - j)];
+            out_q[dst + j] = sq[src + (len - 1 - j)];
+        }
+    }
+}
+
+void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P, const uint64_t *d_off_known,
+                 uint8_t *d_out_bases, uint8_t *d_out_quals, uint64_t *d_out_off, uint64_t *total_out)
+{
+    cudaStream_t st = c->stream;
+    const uint64_t R = S.nreads;
+    if (R >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "too many reads for 32-bit read indices (dataTypeNSeq is uint, parameters.h:82)");
+    if (total_out) *total_out = 0;
+    if (R == 0) {
+        if (d_out_off) BFQ_CUDA(cudaMemsetAsync(d_out_off, 0, 8, st));
+        return;
+    }
+    uint64_t c2b = 0;
+    for (int k = 0; k < 8; k++) c2b |= (uint64_t)S.alpha.code2byte[k] << (8 * k);
+    if (d_off_known) {
+        ProfScope ps(c, PC_WALK, (S.n - R) * (64 + 2));
+        walk_kernel<<<div_up(R, 256), 256, 0, st>>>(S.lines, S.obase, (uint32_t)R, P->max_len, c2b, d_off_known,
+                                                    d_out_bases, d_out_quals, nullptr);
+        BFQ_CUDA(cudaGetLastError());
+        return;
+    }
+    Arena::Mark mk = c->arena.mark();
+    uint8_t *sb = arena_alloc<uint8_t>(c, R * (uint64_t)P->max_len);
+    uint8_t *sq = arena_alloc<uint8_t>(c, R * (uint64_t)P->max_len);
+    uint32_t *lens = arena_alloc<uint32_t>(c, R);
+    const uint32_t nblk = div_up(R, 1024);
+    unsigned long long *blk = arena_alloc<unsigned long long>(c, nblk + 1);
+    {
+        ProfScope ps(c, PC_WALK, (S.n - R) * (64 + 2));
+        walk_kernel<<<div_up(R, 256), 256, 0, st>>>(S.lines, S.obase, (uint32_t)R, P->max_len, c2b, nullptr, sb, sq, lens);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    {
+        ProfScope ps(c, PC_ASSEMBLE, (S.n - R) * 4, 4);
+        scan_reduce_kernel<<<nblk, 256, 0, st>>>(lens, (uint32_t)R, blk);
+        scan_blocks_kernel<<<1, 1024, 0, st>>>(blk, nblk, blk + nblk);
+        scan_down_kernel<<<nblk, 256, 0, st>>>(lens, (uint32_t)R, blk, (unsigned long long *)d_out_off, blk + nblk);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 16, div_up(R * 32, 256));
+        assemble_kernel<<<grid, 256, 0, st>>>(sb, sq, lens, (const unsigned long long *)d_out_off, (uint32_t)R,
+                                              P->max_len, d_out_bases, d_out_quals);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    if (total_out) {
+        BFQ_CUDA(cudaMemcpyAsync(c->h_small, blk + nblk, 8, cudaMemcpyDeviceToHost, st));
+        BFQ_CUDA(cudaStreamSynchronize(st));
+        *total_out = c->h_small[0];
+    } else {
+        BFQ_CUDA(cudaStreamSynchronize(st));
+    }
+    c->arena.release(mk);
+}
+
+} // namespace bfq

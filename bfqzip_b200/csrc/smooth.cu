@@ -1,0 +1,779 @@
+// smooth.cu -- part B on the device: rank/occ "walk lines", positional-cluster detection from the
+// LCP array, quality smoothing and noise reduction.
+//
+// Replaces: src_ext_mem/bfq_ext.cpp buildFreq :132-187,
+// splitIntoPartial/tableOcc :190-348, buildBitVectors :350-412, run :837-948,
+// process_cluster :581-824, modBasesSmoothQS :546-573, buildLF_Cluster :415-476,
+// max_qs/mean_error/avg_qs :479-543; src_ext_mem/decode.cpp computeVectorUnbuildBCR :87-235;
+// external/rankbv (the modified-row bitvector becomes bit 7 of the stored quality byte).
+//
+// The compile-time modes of the reference (-DM=0..3, -DB=0|1, src_ext_mem/makefile:10-22) are
+// compile-time here too: BFQ_M / BFQ_B.
+//
+// HBM layout.  One 64-byte WALK LINE per 32 BWT rows:
+//     u32 cnt[5]   occurrences of codes 1..5 in rows [0, 32*line) PLUS the pile start C[code]
+//                  (so LF(row) = cnt[c-1] + popc(match(c) & below(row)) is one line fetch)
+//     u32 plane[3] bit b of the 3-bit code of each of the 32 rows (row r = bit r)
+//     u8  q[32]    stored quality of each row (smoothed, binned when B=1); bit 7 set when the
+//                  output base differs from the BWT symbol (then obase[row] holds it)
+// so one inverse-LF step (part C) touches exactly one aligned 64-byte line.
+#include "common.cuh"
+#include <math.h>
+#include <algorithm>
+
+namespace bfq {
+
+void byte_histogram(bfq_ctx *c, const uint8_t *d_data, uint64_t n, uint64_t hist_out[256]);
+Alphabet alphabet_from_hist(const uint64_t hist[256], uint8_t eos, bool eos_may_appear);
+
+// ------------------------------------------------------------------ constants for a run
+struct SmoothConst {
+    uint8_t byte2code[256];
+    uint8_t code2byte[8];
+    int32_t K, m, qthr;
+    float fthr;
+    uint8_t default_q;
+    int8_t code_N;
+    uint8_t acgt_mask;
+    uint8_t nsym;
+    uint32_t long_len;
+};
+__constant__ SmoothConst g_sc;
+__constant__ double g_errtab[256];     // pow(10, -(q-33)/10), host glibc (bfq_ext.cpp:532)
+__constant__ double g_m1thr[128];      // g_m1thr[v] = largest x with round(-10*log10(x)) >= v
+
+// decode.cpp:72-84 on an ASCII quality (the caller's `foundQual-33` wraps in uchar like the reference)
+__device__ __forceinline__ uint8_t bin8(uint8_t ascii)
+{
+    uint8_t q = (uint8_t)(ascii - 33);
+    if (q >= 40) q = 40;
+    else if (q >= 35) q = 37;
+    else if (q >= 30) q = 33;
+    else if (q >= 25) q = 27;
+    else if (q >= 20) q = 22;
+    else if (q >= 10) q = 15;
+    else if (q >= 2) q = 6;
+    return (uint8_t)(q + 33);
+}
+// quality byte as stored in a walk line: bit 7 = "base modified", low 7 bits = emitted quality
+__device__ __forceinline__ uint8_t store_q(uint8_t q_with_flag)
+{
+#if BFQ_B
+    return (uint8_t)(bin8(q_with_flag & 0x7F) | (q_with_flag & 0x80));
+#else
+    return q_with_flag;
+#endif
+}
+
+// ------------------------------------------------------------------ walk lines: counts
+constexpr int RK_THREADS = 256;
+constexpr int RK_ROWS = RK_THREADS * 32;     // rows per block (one 32-row group per thread)
+
+__device__ __forceinline__ void load_group_codes(const uint8_t *__restrict__ bwt, uint64_t row0,
+                                                 uint64_t n, const uint8_t *s_lut, uint32_t plane[3],
+                                                 uint32_t cnt[5])
+{
+    plane[0] = plane[1] = plane[2] = 0;
+#pragma unroll
+    for (int k = 0; k < 5; k++) cnt[k] = 0;
+    if (row0 >= n) return;
+    uint8_t b[32];
+    if (row0 + 32 <= n && ((reinterpret_cast<uintptr_t>(bwt) + row0) & 15) == 0) {
+        const uint4 *v = reinterpret_cast<const uint4 *>(bwt + row0);
+        uint4 x0 = v[0], x1 = v[1];
+        uint32_t w[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+        for (int r = 0; r < 32; r++) b[r] = (uint8_t)(w[r >> 2] >> (8 * (r & 3)));
+    } else {
+#pragma unroll
+        for (int r = 0; r < 32; r++) b[r] = (row0 + r < n) ? bwt[row0 + r] : 0;
+    }
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+        uint32_t code = (row0 + r < n) ? s_lut[b[r]] : 0u;
+        plane[0] |= (code & 1u) << r;
+        plane[1] |= ((code >> 1) & 1u) << r;
+        plane[2] |= ((code >> 2) & 1u) << r;
+    }
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        uint32_t c = k + 1;
+        uint32_t mm = ((c & 1) ? plane[0] : ~plane[0]) & ((c & 2) ? plane[1] : ~plane[1]) &
+                      ((c & 4) ? plane[2] : ~plane[2]);
+        cnt[k] = __popc(mm);
+    }
+}
+
+__global__ void __launch_bounds__(RK_THREADS)
+rank_count_kernel(const uint8_t *__restrict__ bwt, uint64_t n, uint32_t *__restrict__ blk_counts)
+{
+    __shared__ uint8_t s_lut[256];
+    __shared__ uint32_t s_cnt[5];
+    s_lut[threadIdx.x] = g_sc.byte2code[threadIdx.x];
+    if (threadIdx.x < 5) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t plane[3], cnt[5];
+    load_group_codes(bwt, (uint64_t)blockIdx.x * RK_ROWS + (uint64_t)threadIdx.x * 32, n, s_lut, plane, cnt);
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        uint32_t v = cnt[k];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_cnt[k], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < 5) blk_counts[(size_t)blockIdx.x * 8 + threadIdx.x] = s_cnt[threadIdx.x];
+}
+
+// single block: exclusive scan over blocks for each code, plus the pile start C[code]
+__global__ void __launch_bounds__(1024)
+rank_scan_kernel(uint32_t *__restrict__ blk_counts, uint32_t nblk, const uint32_t *__restrict__ pile_start)
+{
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int k = 0; k < 5; k++) {
+        if (tid == 0) s_carry = pile_start[k];
+        __syncthreads();
+        for (uint32_t base = 0; base < nblk; base += 1024) {
+            uint32_t i = base + tid;
+            uint32_t v = i < nblk ? blk_counts[(size_t)i * 8 + k] : 0, x = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+            if (lane == 31) s_warp[w] = x;
+            __syncthreads();
+            uint32_t add = 0;
+            for (int j = 0; j < w; j++) add += s_warp[j];
+            uint32_t carry = s_carry;
+            if (i < nblk) blk_counts[(size_t)i * 8 + k] = carry + add + x - v;
+            __syncthreads();
+            if (tid == 1023) s_carry = carry + add + x;
+            __syncthreads();
+        }
+    }
+}
+
+__global__ void __launch_bounds__(RK_THREADS)
+rank_build_kernel(const uint8_t *__restrict__ bwt, uint64_t n, const uint32_t *__restrict__ blk_base,
+                  uint8_t *__restrict__ lines)
+{
+    __shared__ uint8_t s_lut[256];
+    __shared__ uint32_t s_warp[RK_THREADS / 32][5];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    s_lut[tid] = g_sc.byte2code[tid];
+    __syncthreads();
+    const uint64_t row0 = (uint64_t)blockIdx.x * RK_ROWS + (uint64_t)tid * 32;
+    uint32_t plane[3], cnt[5], excl[5];
+    load_group_codes(bwt, row0, n, s_lut, plane, cnt);
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        uint32_t x = cnt[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) s_warp[w][k] = x;
+        excl[k] = x - cnt[k];
+    }
+    __syncthreads();
+    if (row0 >= n) return;
+#pragma unroll
+    for (int k = 0; k < 5; k++) {
+        uint32_t add = blk_base[(size_t)blockIdx.x * 8 + k];
+        for (int j = 0; j < w; j++) add += s_warp[j][k];
+        excl[k] += add;
+    }
+    uint4 *L = reinterpret_cast<uint4 *>(lines + (row0 >> 5) * 64);
+    L[0] = make_uint4(excl[0], excl[1], excl[2], excl[3]);
+    L[1] = make_uint4(excl[4], plane[0], plane[1], plane[2]);
+}
+
+// ------------------------------------------------------------------ line access helpers
+struct LineHdr { uint32_t cnt[5]; uint32_t plane[3]; };
+
+__device__ __forceinline__ LineHdr load_hdr(const uint8_t *__restrict__ lines, uint64_t row)
+{
+    const uint4 *L = reinterpret_cast<const uint4 *>(lines + (row >> 5) * 64);
+    uint4 a = L[0], b = L[1];
+    LineHdr h;
+    h.cnt[0] = a.x; h.cnt[1] = a.y; h.cnt[2] = a.z; h.cnt[3] = a.w; h.cnt[4] = b.x;
+    h.plane[0] = b.y; h.plane[1] = b.z; h.plane[2] = b.w;
+    return h;
+}
+__device__ __forceinline__ uint32_t hdr_code(const LineHdr &h, uint32_t r)
+{
+    return ((h.plane[0] >> r) & 1u) | (((h.plane[1] >> r) & 1u) << 1) | (((h.plane[2] >> r) & 1u) << 2);
+}
+__device__ __forceinline__ uint32_t hdr_lf(const LineHdr &h, uint32_t r, uint32_t c)   // c in 1..5
+{
+    uint32_t mm = ((c & 1) ? h.plane[0] : ~h.plane[0]) & ((c & 2) ? h.plane[1] : ~h.plane[1]) &
+                  ((c & 4) ? h.plane[2] : ~h.plane[2]);
+    return h.cnt[c - 1] + __popc(mm & ((1u << r) - 1u));
+}
+__device__ __forceinline__ uint8_t *line_q(uint8_t *lines, uint64_t row)
+{
+    return lines + (row >> 5) * 64 + 32 + (row & 31);
+}
+
+// ------------------------------------------------------------------ cluster rules (shared)
+// Device counters: 0 clusters 1 discarded 2 ambiguous 3 processed 4 bases_inside
+//                  5 qs_smoothed 6 modified 7 error(>2 frequent symbols)
+enum { ST_CLUSTERS = 0, ST_DISCARDED, ST_AMBIGUOUS, ST_PROCESSED, ST_BASES, ST_SMOOTHED, ST_MODIFIED, ST_ERR, ST_COUNT };
+
+struct ClAcc {                     // per-cluster accumulators (rule 8, bfq_ext.cpp:612-654)
+    uint32_t freq[6];              // by code; [0] unused
+    uint32_t hiq;                  // bit c: some row with code c has q >= qthr+33 ("lowQS" in the reference)
+    uint32_t base_num;
+    uint32_t mx;                   // M=0
+    int32_t isum;                  // M=3 (int, wraps like the reference's)
+    double dsum;                   // M=1, added in row order
+};
+
+enum { ACT_NONE = 0, ACT_RULE10 = 1, ACT_RULE11 = 2 };
+struct Decision { int act; uint32_t sym, f0, f1; uint8_t newqs; };
+
+__device__ __forceinline__ uint8_t newqs_from(const ClAcc &a)
+{
+#if BFQ_M == 0
+    return (uint8_t)a.mx;                                            // bfq_ext.cpp:502-518
+#elif BFQ_M == 1
+    // bfq_ext.cpp:537-541: (uchar)round(-10*log10(sum/num)) + 33, through host-built thresholds
+    double avg = __ddiv_rn(a.dsum, (double)a.base_num);
+    int lo = 0, hi = 127;                                            // largest v with avg <= thr[v]
+    while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (avg <= g_m1thr[mid]) lo = mid; else hi = mid - 1; }
+    return (uint8_t)(lo + 33);
+#elif BFQ_M == 2
+    return g_sc.default_q;                                           // bfq_ext.cpp:648
+#else
+    if (a.isum == 0) return 0;                                       // bfq_ext.cpp:495-496
+    float f = __fdiv_rn((float)a.isum, (float)(unsigned long long)a.base_num);
+    return (uint8_t)(int)floor((double)f + 0.5);
+#endif
+}
+
+// rules 7-9 (bfq_ext.cpp:584, 633, 665-713).  st[] are this thread's counters.
+__device__ __forceinline__ Decision decide(uint32_t len, const ClAcc &a, uint32_t *st)
+{
+    Decision d{ACT_NONE, 0, 0, 0, 0};
+    if ((int)len < g_sc.m) return d;
+    if (a.base_num == 0) return d;
+    st[ST_CLUSTERS]++;
+    st[ST_BASES] += a.base_num;
+    d.newqs = newqs_from(a);
+    uint32_t F[3]; int nF = 0;
+#pragma unroll
+    for (uint32_t c = 1; c <= 5; c++) {
+        if (a.freq[c] > 0) {
+            uint8_t perc = (uint8_t)((100ull * a.freq[c]) / a.base_num);
+            if ((float)perc >= g_sc.fthr) { if (nF < 3) F[nF] = c; nF++; }
+        }
+    }
+    if (nF >= 3) { st[ST_ERR]++; return d; }
+    const uint32_t cN = (uint32_t)(int)g_sc.code_N;
+    if (nF == 0) st[ST_DISCARDED]++;
+    else if (nF == 1) {
+        if (F[0] == cN) st[ST_DISCARDED]++;
+        else { d.act = ACT_RULE10; d.sym = F[0]; st[ST_PROCESSED]++; }
+    } else if (a.base_num < (uint32_t)g_sc.m) st[ST_DISCARDED]++;
+    else if (F[0] == cN) { d.act = ACT_RULE10; d.sym = F[1]; st[ST_PROCESSED]++; }
+    else if (F[1] == cN) { d.act = ACT_RULE10; d.sym = F[0]; st[ST_PROCESSED]++; }
+    else { d.act = ACT_RULE11; d.f0 = F[0]; d.f1 = F[1]; }
+    return d;
+}
+
+// rule 10 on one row (bfq_ext.cpp:546-573).  Returns the stored byte (bit 7 = modified).
+__device__ __forceinline__ uint8_t rule10_row(uint32_t c, uint8_t q, uint32_t sym, uint32_t hiq,
+                                              uint8_t newqs, uint32_t *st)
+{
+    if (c == 0) return q;
+    if (c != sym && !((hiq >> c) & 1u)) { st[ST_MODIFIED]++; return (uint8_t)(q | 0x80); }
+    if (c == sym) { st[ST_SMOOTHED]++; return newqs; }
+    if (newqs < q) { st[ST_SMOOTHED]++; return newqs; }
+    return q;
+}
+
+__device__ __forceinline__ void acc_row(ClAcc &a, uint32_t c, uint8_t q)
+{
+    if (c == 0) return;
+    a.freq[c]++;
+    a.base_num++;
+    if ((int)q >= g_sc.qthr + 33) a.hiq |= 1u << c;
+#if BFQ_M == 0
+    a.mx = max(a.mx, (uint32_t)q);
+#elif BFQ_M == 1
+    a.dsum = __dadd_rn(a.dsum, g_errtab[q]);
+#elif BFQ_M == 3
+    a.isum += (int32_t)q;
+#endif
+}
+
+// rule 5-6 flag of row i (bfq_ext.cpp:375-392, 880): lcp[i] >= K and row i is not a local minimum
+__device__ __forceinline__ bool f_flag(int lm1, int l0, int lp1, bool is_first, bool is_last)
+{
+    if (is_first) return false;
+    bool thr = l0 >= g_sc.K;
+    bool mn = !is_last && (lm1 > l0) && (l0 <= lp1);
+    return thr && !mn;
+}
+
+struct R11Desc { uint32_t start, len, packed /* f0 | f1<<8 | newqs<<16 | hiq<<24 */, pad; };
+
+struct SmoothLists {
+    uint32_t *long_starts;   uint32_t *long_count;   uint32_t long_cap;
+    R11Desc *r11;            uint32_t *r11_count;    uint32_t r11_cap;
+    unsigned long long *stats;                        // ST_COUNT counters
+};
+
+// ------------------------------------------------------------------ tile kernel (rules 5-10)
+// One block stages CL_TILE rows of bwt/qs/lcp in shared memory, finds the clusters that START
+// in the tile, and one thread walks each cluster (cluster lengths are ~5-40 rows; clusters longer
+// than g_sc.long_len rows go to cluster_long_kernel, two-base clusters to rule11_kernel).
+// A tile writes the stored quality of every row it owns: all rows except its leading run of
+// flagged rows (those belong to a cluster that started in an earlier tile, whose owner writes them).
+constexpr int CL_THREADS = 256;
+constexpr int CL_TILE = 4096;
+
+__device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stats, unsigned long long *g_stats)
+{
+    // caller zeroed s_stats and synchronised before; all threads of the block call this
+#pragma unroll
+    for (int k = 0; k < ST_COUNT; k++) {
+        uint32_t v = st[k];
+#pragma unroll
+        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_stats[k], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < ST_COUNT && s_stats[threadIdx.x])
+        atomicAdd(&g_stats[threadIdx.x], (unsigned long long)s_stats[threadIdx.x]);
+}
+
+__global__ void __launch_bounds__(CL_THREADS)
+cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
+                    const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
+                    uint8_t *__restrict__ obase, SmoothLists L)
+{
+    __shared__ uint8_t s_lcp[CL_TILE + 8];      // s_lcp[r + 1] = lcp[t0 + r], r = -1 .. CL_TILE + 1
+    __shared__ uint8_t s_code[CL_TILE];
+    __shared__ uint8_t s_q[CL_TILE];
+    __shared__ uint16_t s_starts[CL_TILE / 2 + 2];
+    __shared__ uint32_t s_nstarts, s_lead;
+    __shared__ uint8_t s_lut[256];
+    __shared__ uint32_t s_stats[ST_COUNT];
+
+    const int tid = threadIdx.x;
+    const int64_t t0 = (int64_t)blockIdx.x * CL_TILE;
+    const int64_t nn = (int64_t)n;
+    s_lut[tid] = g_sc.byte2code[tid];
+    if (tid == 0) { s_nstarts = 0; s_lead = CL_TILE; }
+    if (tid < ST_COUNT) s_stats[tid] = 0;
+    __syncthreads();
+    for (int r = tid; r < CL_TILE + 3; r += CL_THREADS) {
+        int64_t i = t0 + r - 1;
+        s_lcp[r] = (i >= 0 && i < nn) ? lcp[i] : 0;
+    }
+    for (int r = tid; r < CL_TILE; r += CL_THREADS) {
+        int64_t i = t0 + r;
+        bool ok = i < nn;
+        s_code[r] = ok ? s_lut[bwt[i]] : 0;
+        s_q[r] = ok ? qs[i] : 0;
+    }
+    __syncthreads();
+
+    auto lcp_at = [&](int64_t i) -> int {
+        if (i < 0 || i >= nn) return 0;
+        int64_t r = i - t0 + 1;
+        if (r >= 0 && r < CL_TILE + 3) return s_lcp[r];
+        return lcp[i];
+    };
+    auto F = [&](int64_t i) -> bool {
+        if (i <= 0 || i >= nn) return false;
+        return f_flag(lcp_at(i - 1), lcp_at(i), lcp_at(i + 1), false, i == nn - 1);
+    };
+
+    // ---- cluster starts and the leading run
+    for (int r = tid; r < CL_TILE; r += CL_THREADS) {
+        int64_t i = t0 + r;
+        if (i >= nn) break;
+        bool fi = F(i);
+        if (!fi) {
+            atomicMin(&s_lead, (uint32_t)r);
+            if (F(i + 1)) s_starts[atomicAdd(&s_nstarts, 1u)] = (uint16_t)r;
+        }
+    }
+    __syncthreads();
+    const uint32_t nstarts = s_nstarts;
+    const uint32_t long_len = g_sc.long_len;
+    uint32_t st[ST_COUNT];
+#pragma unroll
+    for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
+
+    for (uint32_t idx = tid; idx < nstarts; idx += CL_THREADS) {
+        const int64_t a = t0 + s_starts[idx];
+        int64_t e = a + 1;
+        while ((uint64_t)(e - a) <= long_len && F(e)) e++;
+        const uint32_t len = (uint32_t)(e - a);
+        if (len > long_len) {                                  // still open: hand over
+            uint32_t k = atomicAdd(L.long_count, 1u);
+            if (k < L.long_cap) L.long_starts[k] = (uint32_t)a;
+            continue;
+        }
+        const int64_t tile_end = t0 + CL_TILE;
+        // pass 1: statistics (rule 8)
+        unsigned long long fpack = 0;                          // 12-bit counters per code (len < 4096)
+        ClAcc acc;
+        acc.hiq = 0; acc.base_num = 0; acc.mx = 0; acc.isum = 0; acc.dsum = 0.0;
+        for (int64_t i = a; i < e; i++) {
+            uint32_t c; uint8_t q;
+            if (i < tile_end) { c = s_code[i - t0]; q = s_q[i - t0]; }
+            else { c = s_lut[bwt[i]]; q = qs[i]; }
+            if (c) {
+                fpack += 1ull << (12 * c);
+                acc.base_num++;
+                if ((int)q >= g_sc.qthr + 33) acc.hiq |= 1u << c;
+#if BFQ_M == 0
+                acc.mx = max(acc.mx, (uint32_t)q);
+#elif BFQ_M == 1
+                acc.dsum = __dadd_rn(acc.dsum, g_errtab[q]);
+#elif BFQ_M == 3
+                acc.isum += (int32_t)q;
+#endif
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 6; c++) acc.freq[c] = (uint32_t)(fpack >> (12 * c)) & 0xFFFu;
+        Decision d = decide(len, acc, st);
+        if (d.act == ACT_RULE11) {
+            uint32_t k = atomicAdd(L.r11_count, 1u);
+            if (k < L.r11_cap)
+                L.r11[k] = R11Desc{(uint32_t)a, len, d.f0 | (d.f1 << 8) | ((uint32_t)d.newqs << 16) | (acc.hiq << 24), 0};
+        }
+        if (d.act != ACT_RULE10 && e <= tile_end) continue;     // nothing changes, all rows in tile
+        // pass 2: apply rule 10 / write the rows that lie beyond this tile
+        const uint8_t symb = g_sc.code2byte[d.sym];
+        for (int64_t i = a; i < e; i++) {
+            const bool in_tile = i < tile_end;
+            uint32_t c; uint8_t q;
+            if (in_tile) { c = s_code[i - t0]; q = s_q[i - t0]; }
+            else { c = s_lut[bwt[i]]; q = qs[i]; }
+            uint8_t o = q;
+            if (d.act == ACT_RULE10) o = rule10_row(c, q, d.sym, acc.hiq, d.newqs, st);
+            if (o & 0x80) obase[i] = symb;
+            if (in_tile) { if (o != q) s_q[i - t0] = o; }
+            else *line_q(lines, (uint64_t)i) = store_q(o);
+        }
+    }
+    __syncthreads();
+    // ---- stored qualities of the rows this tile owns
+    const uint32_t lead = s_lead;
+    for (int r = tid; r < CL_TILE; r += CL_THREADS) {
+        int64_t i = t0 + r;
+        if (i < nn && (uint32_t)r >= lead) *line_q(lines, (uint64_t)i) = store_q(s_q[r]);
+    }
+    flush_stats(st, s_stats, L.stats);
+}
+
+// ------------------------------------------------------------------ long clusters: one block each
+__global__ void __launch_bounds__(CL_THREADS)
+cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
+                    const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
+                    uint8_t *__restrict__ obase, SmoothLists L)
+{
+    __shared__ uint8_t s_lut[256];
+    __shared__ uint32_t s_stats[ST_COUNT];
+    __shared__ uint32_t s_end;
+    __shared__ uint32_t s_freq[6], s_hiq, s_base, s_mx, s_isum;
+    __shared__ double s_dsum;
+    __shared__ Decision s_dec;
+    __shared__ uint8_t s_c[1024], s_qq[1024];
+    const int tid = threadIdx.x;
+    const int64_t nn = (int64_t)n;
+    s_lut[tid] = g_sc.byte2code[tid];
+    if (tid < ST_COUNT) s_stats[tid] = 0;
+    __syncthreads();
+    uint32_t st[ST_COUNT];
+#pragma unroll
+    for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
+
+    auto lcp_at = [&](int64_t i) -> int { return (i < 0 || i >= nn) ? 0 : (int)lcp[i]; };
+    auto F = [&](int64_t i) -> bool {
+        if (i <= 0 || i >= nn) return false;
+        return f_flag(lcp_at(i - 1), lcp_at(i), lcp_at(i + 1), false, i == nn - 1);
+    };
+    const uint32_t count = min(*L.long_count, L.long_cap);
+    for (uint32_t ci = blockIdx.x; ci < count; ci += gridDim.x) {
+        const int64_t a = L.long_starts[ci];
+        // ---- end of the run: first e > a with !F(e)
+        if (tid == 0) s_end = 0xFFFFFFFFu;
+        __syncthreads();
+        for (int64_t base = a + 1;; base += CL_THREADS) {
+            int64_t i = base + tid;
+            if (i <= nn && !F(i)) atomicMin(&s_end, (uint32_t)i);     // F(nn) is false
+            __syncthreads();
+            if (s_end != 0xFFFFFFFFu) break;
+            __syncthreads();
+        }
+        const int64_t e = s_end;
+        const uint32_t len = (uint32_t)(e - a);
+        // ---- statistics
+        if (tid < 6) s_freq[tid] = 0;
+        if (tid == 0) { s_hiq = 0; s_base = 0; s_mx = 0; s_isum = 0; s_dsum = 0.0; }
+        __syncthreads();
+        {
+            uint32_t f[6] = {0, 0, 0, 0, 0, 0}, hiq = 0, mx = 0, isum = 0;
+            for (int64_t i = a + tid; i < e; i += CL_THREADS) {
+                uint32_t c = s_lut[bwt[i]]; uint8_t q = qs[i];
+                if (!c) continue;
+#pragma unroll
+                for (uint32_t k = 1; k < 6; k++) f[k] += (c == k);
+                if ((int)q >= g_sc.qthr + 33) hiq |= 1u << c;
+                mx = max(mx, (uint32_t)q);
+                isum += q;
+            }
+#pragma unroll
+            for (int k = 1; k < 6; k++) if (f[k]) { atomicAdd(&s_freq[k], f[k]); atomicAdd(&s_base, f[k]); }
+            if (hiq) atomicOr(&s_hiq, hiq);
+            atomicMax(&s_mx, mx);
+            atomicAdd(&s_isum, isum);          // wraps mod 2^32 exactly like the reference's int
+        }
+#if BFQ_M == 1
+        // the reference adds the error probabilities in row order, in double: keep that order
+        for (int64_t base = a; base < e; base += 1024) {
+            __syncthreads();
+            for (int r = tid; r < 1024; r += CL_THREADS) {
+                int64_t i = base + r;
+                if (i < e) { s_c[r] = s_lut[bwt[i]]; s_qq[r] = qs[i]; }
+            }
+            __syncthreads();
+            if (tid == 0) {
+                double s = s_dsum;
+                int lim = (int)min((int64_t)1024, e - base);
+                for (int r = 0; r < lim; r++) if (s_c[r]) s = __dadd_rn(s, g_errtab[s_qq[r]]);
+                s_dsum = s;
+            }
+        }
+#endif
+        __syncthreads();
+        if (tid == 0) {
+            ClAcc acc;
+#pragma unroll
+            for (int k = 0; k < 6; k++) acc.freq[k] = s_freq[k];
+            acc.hiq = s_hiq; acc.base_num = s_base; acc.mx = s_mx; acc.isum = (int32_t)s_isum; acc.dsum = s_dsum;
+            Decision d = decide(len, acc, st);
+            if (d.act == ACT_RULE11) {
+                uint32_t k = atomicAdd(L.r11_count, 1u);
+                if (k < L.r11_cap)
+                    L.r11[k] = R11Desc{(uint32_t)a, len, d.f0 | (d.f1 << 8) | ((uint32_t)d.newqs << 16) | (acc.hiq << 24), 0};
+            }
+            s_dec = d;
+        }
+        __syncthreads();
+        const Decision d = s_dec;
+        const uint32_t hiq = s_hiq;
+        const uint8_t symb = g_sc.code2byte[d.sym];
+        // ---- every row of a long cluster is written here (later tiles skipped them)
+        for (int64_t i = a + tid; i < e; i += CL_THREADS) {
+            uint32_t c = s_lut[bwt[i]]; uint8_t q = qs[i];
+            uint8_t o = q;
+            if (d.act == ACT_RULE10) o = rule10_row(c, q, d.sym, hiq, d.newqs, st);
+            if (o & 0x80) obase[i] = symb;
+            *line_q(lines, (uint64_t)i) = store_q(o);
+        }
+        __syncthreads();
+    }
+    flush_stats(st, s_stats, L.stats);
+}
+
+// ------------------------------------------------------------------ rule 11: two frequent bases
+// bfq_ext.cpp:713-802 with buildLF_Cluster :415-476.  One warp per cluster; the symbol that
+// precedes row j in its read is bwt[LF(j)], two walk-line fetches.
+__global__ void __launch_bounds__(256)
+rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8_t *__restrict__ obase,
+              SmoothLists L)
+{
+    __shared__ uint32_t s_stats[ST_COUNT];
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < ST_COUNT) s_stats[tid] = 0;
+    __syncthreads();
+    uint32_t st[ST_COUNT];
+#pragma unroll
+    for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
+    const uint32_t count = min(*L.r11_count, L.r11_cap);
+    const uint32_t warp0 = (blockIdx.x * 256u + tid) >> 5, nwarps = (gridDim.x * 256u) >> 5;
+    const uint32_t acgt = g_sc.acgt_mask;
+    for (uint32_t di = warp0; di < count; di += nwarps) {
+        const R11Desc D = L.r11[di];
+        const uint32_t f0 = D.packed & 255u, f1 = (D.packed >> 8) & 255u, hiq = D.packed >> 24;
+        const uint8_t newqs = (uint8_t)(D.packed >> 16);
+        uint32_t P0 = 0, P1 = 0;
+        for (uint32_t j = lane; j < D.len; j += 32) {
+            const uint64_t i = (uint64_t)D.start + j;
+            LineHdr h = load_hdr(lines, i);
+            uint32_t c = hdr_code(h, (uint32_t)(i & 31));
+            if (c == f0 || c == f1) {
+                uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
+                LineHdr h2 = load_hdr(lines, r);
+                uint32_t pc = hdr_code(h2, (uint32_t)(r & 31));
+                if ((acgt >> pc) & 1u) { if (c == f0) P0 |= 1u << pc; else P1 |= 1u << pc; }
+            }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) { P0 |= __shfl_xor_sync(0xffffffffu, P0, o); P1 |= __shfl_xor_sync(0xffffffffu, P1, o); }
+        const bool ok = __popc(P0) == 1 && __popc(P1) == 1 && P0 != P1;
+        if (!ok) { if (lane == 0) st[ST_AMBIGUOUS]++; continue; }
+        if (lane == 0) st[ST_PROCESSED]++;
+        const uint32_t prec0 = __ffs(P0) - 1, prec1 = __ffs(P1) - 1;
+        for (uint32_t j = lane; j < D.len; j += 32) {
+            const uint64_t i = (uint64_t)D.start + j;
+            LineHdr h = load_hdr(lines, i);
+            uint32_t c = hdr_code(h, (uint32_t)(i & 31));
+            if (c == 0) continue;
+            const uint8_t q = qs[i];
+            if (c != f0 && c != f1 && !((hiq >> c) & 1u)) {
+                uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
+                LineHdr h2 = load_hdr(lines, r);
+                uint32_t pc = hdr_code(h2, (uint32_t)(r & 31));
+                uint32_t to = pc == prec0 ? f0 : (pc == prec1 ? f1 : 0u);
+                if (to) {
+                    obase[i] = g_sc.code2byte[to];
+                    *line_q(lines, i) = store_q((uint8_t)(q | 0x80));
+                    st[ST_MODIFIED]++;
+                }
+            } else if (c == f0 || c == f1) {
+                *line_q(lines, i) = store_q(newqs);
+                st[ST_SMOOTHED]++;
+            } else if (newqs < q) {
+                *line_q(lines, i) = store_q(newqs);
+                st[ST_SMOOTHED]++;
+            }
+        }
+    }
+    flush_stats(st, s_stats, L.stats);
+}
+
+// ------------------------------------------------------------------ host side
+// M=1 tables, computed with the host libm the reference itself links (bfq_ext.cpp:532, 539).
+static void build_m1_tables(double errtab[256], double thr[128])
+{
+    for (int q = 0; q < 256; q++) errtab[q] = pow(10, -((double)q - 33.0) / 10.0);
+    auto pred = [](double x, int v) { return round(-10 * log10(x)) >= (double)v; };
+    thr[0] = INFINITY;
+    for (int v = 1; v < 128; v++) {
+        // largest double x with round(-10*log10(x)) >= v; the predicate is monotone in x
+        double lo = 1e-300, hi = 1e10;                 // pred(lo) true, pred(hi) false
+        uint64_t a, b;
+        memcpy(&a, &lo, 8); memcpy(&b, &hi, 8);
+        while (b - a > 1) {
+            uint64_t mid = a + (b - a) / 2; double x;
+            memcpy(&x, &mid, 8);
+            if (pred(x, v)) a = mid; else b = mid;
+        }
+        memcpy(&thr[v], &a, 8);
+    }
+}
+
+static void launch_check(bfq_ctx *c) { BFQ_CUDA(cudaGetLastError()); (void)c; }
+
+void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
+                uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats)
+{
+    cudaStream_t st = c->stream;
+    if (n >= ((uint64_t)1 << 32) - 64) BFQ_FAIL(BFQ_ETOOLARGE, "BWT has %llu rows; this build indexes rows with 32 bits", (unsigned long long)n);
+    if (P->max_len <= 0 || P->max_len > 255) BFQ_FAIL(BFQ_EINVAL, "max_len must be 1..255 (dataTypelenSeq is uchar, parameters.h:68)");
+
+    // ---- buildFreq (bfq_ext.cpp:132-187): symbol counts, alphabet in byte order, pile starts
+    uint64_t hist[256], qhist[256];
+    byte_histogram(c, d_bwt, n, hist);
+    byte_histogram(c, d_qs, n, qhist);
+    for (int b = 128; b < 256; b++)
+        if (qhist[b]) BFQ_FAIL(BFQ_EINVAL, "quality byte %d >= 128 is not a FASTQ quality", b);
+    Alphabet A = alphabet_from_hist(hist, P->eos_byte, /*eos_may_appear=*/true);
+    out->alpha = A;
+    out->n = n;
+    out->nreads = hist[P->eos_byte];
+
+    SmoothConst sc;
+    memset(&sc, 0, sizeof sc);
+    for (int b = 0; b < 256; b++) sc.byte2code[b] = A.byte2code[b] == 0xFF ? 0 : A.byte2code[b];
+    memcpy(sc.code2byte, A.code2byte, 8);
+    sc.K = P->K; sc.m = P->m; sc.qthr = P->qthr; sc.fthr = P->fthr;
+    sc.default_q = P->default_q; sc.code_N = (int8_t)A.code_N; sc.acgt_mask = A.acgt_mask;
+    sc.nsym = (uint8_t)A.nsym;
+    sc.long_len = (uint32_t)std::min<int64_t>(c->opt_long_cluster, 4000);
+    BFQ_CUDA(cudaMemcpyToSymbolAsync(g_sc, &sc, sizeof sc, 0, cudaMemcpyHostToDevice, st));
+#if BFQ_M == 1
+    {
+        static double errtab[256], thr[128];
+        static bool built = false;
+        if (!built) { build_m1_tables(errtab, thr); built = true; }
+        BFQ_CUDA(cudaMemcpyToSymbolAsync(g_errtab, errtab, sizeof errtab, 0, cudaMemcpyHostToDevice, st));
+        BFQ_CUDA(cudaMemcpyToSymbolAsync(g_m1thr, thr, sizeof thr, 0, cudaMemcpyHostToDevice, st));
+    }
+#endif
+    uint32_t *d_pile = (uint32_t *)((char *)c->d_small + 2048);
+    {
+        uint32_t pile[8] = {0};
+        uint64_t acc = hist[P->eos_byte];
+        for (int k = 1; k <= 5; k++) { pile[k - 1] = (uint32_t)acc; if (k <= A.nsym) acc += hist[A.code2byte[k]]; }
+        uint32_t *h = (uint32_t *)((char *)c->h_small + 2048);
+        memcpy(h, pile, sizeof pile);
+        BFQ_CUDA(cudaMemcpyAsync(d_pile, h, sizeof pile, cudaMemcpyHostToDevice, st));
+    }
+    BFQ_CUDA(cudaStreamSynchronize(st));     // the pageable/pinned staging above is reused by later calls
+
+    // ---- walk lines (computeVectorUnbuildBCR, decode.cpp:87-235, + tableOcc)
+    const uint64_t nlines = (n + 31) / 32;
+    out->lines = arena_alloc<uint8_t>(c, nlines * 64 + 64);
+    out->obase = arena_alloc<uint8_t>(c, n + 64);
+    Arena::Mark mk = c->arena.mark();
+    const uint32_t nblk = div_up(n, RK_ROWS);
+    uint32_t *blk = arena_alloc<uint32_t>(c, (size_t)nblk * 8);
+    {
+        ProfScope ps(c, PC_RANK, 2 * n + nlines * 32, 3);
+        rank_count_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, blk);
+        rank_scan_kernel<<<1, 1024, 0, st>>>(blk, nblk, d_pile);
+        rank_build_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, blk, out->lines);
+        launch_check(c);
+    }
+
+    // ---- clusters
+    SmoothLists L;
+    L.long_cap = (uint32_t)(n / std::max<uint32_t>(sc.long_len, 1) + 1024);
+    L.r11_cap = (uint32_t)(n / 8 + 1024);
+    L.long_starts = arena_alloc<uint32_t>(c, L.long_cap);
+    L.r11 = arena_alloc<R11Desc>(c, L.r11_cap);
+    unsigned long long *d_stats = arena_alloc<unsigned long long>(c, ST_COUNT + 2);
+    L.stats = d_stats;
+    L.long_count = (uint32_t *)(d_stats + ST_COUNT);
+    L.r11_count = L.long_count + 1;
+    BFQ_CUDA(cudaMemsetAsync(d_stats, 0, (ST_COUNT + 2) * 8, st));
+    {
+        ProfScope ps(c, PC_CLUSTER, 4 * n);
+        cluster_tile_kernel<<<div_up(n, CL_TILE), CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        launch_check(c);
+    }
+    {
+        ProfScope ps(c, PC_CLUSTER_LONG, 0);
+        cluster_long_kernel<<<c->num_sms * 2, CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        launch_check(c);
+    }
+    {
+        ProfScope ps(c, PC_RULE11, 0);
+        rule11_kernel<<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L);
+        launch_check(c);
+    }
+    BFQ_CUDA(cudaMemcpyAsync(c->h_small, d_stats, (ST_COUNT + 2) * 8, cudaMemcpyDeviceToHost, st));
+    BFQ_CUDA(cudaStreamSynchronize(st));
+    const uint64_t *h = c->h_small;
+    const uint32_t *cnts = (const uint32_t *)(h + ST_COUNT);
+    c->arena.release(mk);
+    if (cnts[0] > L.long_cap || cnts[1] > L.r11_cap)
+        BFQ_FAIL(BFQ_ECAPACITY, "internal cluster list overflow (long %u/%u, two-base %u/%u)", cnts[0], L.long_cap, cnts[1], L.r11_cap);
+    if (h[ST_ERR])
+        BFQ_FAIL(BFQ_EFREQ3, "a cluster has more than two frequent symbols (the reference asserts, bfq_ext.cpp:683); raise -f");
+    if (stats) {
+        stats->clusters = h[ST_CLUSTERS]; stats->discarded = h[ST_DISCARDED]; stats->ambiguous = h[ST_AMBIGUOUS];
+        stats->processed = h[ST_PROCESSED]; stats->bases_inside = h[ST_BASES]; stats->qs_smoothed = h[ST_SMOOTHED];
+        stats->modified = h[ST_MODIFIED]; stats->nreads = out->nreads; stats->n = n;
+    }
+}
+
+} // namespace bfq

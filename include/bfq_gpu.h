@@ -1,0 +1,141 @@
+/* bfq_gpu.h -- C ABI of the B200-native BFQzip data path (libbfqgpu_M<M>_B<B>.so).
+ *
+ * The reference has no in-process API for this path: BFQzip_ext.py runs two tools as
+ * subprocesses and exchanges flat files (BFQzip_ext.py:173-177, 207-215, 310-318).  The
+ * entry points below are what the two drop-in tools (tools/gsufsort_gpu.cpp, tools/bfq_ext_gpu.cpp)
+ * bind, and what a maintainer would bind from the reference's own C/C++ tools:
+ *
+ *   bfq_build_ebwt      replaces  gsufsort's load + cat_all + gsacak + store_to_disk
+ *                       (external/gsufsort/main.c:280-311, 476-486, 848-895;
+ *                        external/gsufsort/lib/utils.c:193-249; external/gsacak.c:2503-2518)
+ *                       == eGap's three phases (external/egap/eGap:255-365) up to the EOS byte.
+ *   bfq_smooth_rebuild  replaces  bfq_ext main phases 1-5 (src_ext_mem/bfq_ext.cpp:1067-1106):
+ *                       buildFreq, splitIntoPartial, computeVectorUnbuildBCR, buildBitVectors,
+ *                       run/process_cluster, BCRInverse (src_ext_mem/decode.cpp:238-317).
+ *   bfq_pipeline        both, fused on the device (no file / host round trip in between).
+ *
+ * Compile-time modes: the reference selects the smoothing rule with -DM=0..3 and Illumina
+ * binning with -DB=0|1 (src_ext_mem/makefile:10-22, bfq_ext.cpp:643-654, parameters.h:41-45),
+ * one binary per mode.  Likewise there is one shared object per (M,B); bfq_mode_M/B report it.
+ *
+ * Conventions: plain C types only; every function returns 0 on success or a negative
+ * BFQ_E* code, with a message available from bfq_last_error() (thread-local).  There is no
+ * CPU fallback: without a CUDA device bfq_ctx_create fails with BFQ_ENODEVICE.
+ * A bfq_ctx owns one device, one stream and a device arena; it is not thread-safe -- use one
+ * ctx per host thread / per GPU (BFQzip_parallel.py:102-119 runs one tool process per block).
+ */
+#ifndef BFQ_GPU_H
+#define BFQ_GPU_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BFQ_OK          0
+#define BFQ_ENODEVICE  -1   /* no CUDA device / CUDA runtime error at start-up        */
+#define BFQ_ECUDA      -2   /* CUDA error during a call                                */
+#define BFQ_EINVAL     -3   /* bad argument (null pointer, size, offsets)              */
+#define BFQ_EALPHABET  -4   /* more than 5 distinct non-EOS symbols, or a base byte <= EOS */
+#define BFQ_ETOOLARGE  -5   /* collection does not fit this build's 32-bit row indices */
+#define BFQ_EFREQ3     -6   /* >2 frequent symbols in a cluster: the reference asserts (bfq_ext.cpp:683) */
+#define BFQ_ENOMEM     -7   /* device or host allocation failed                        */
+#define BFQ_ECAPACITY  -8   /* caller-provided output capacity too small               */
+
+typedef struct bfq_ctx bfq_ctx;
+
+/* Run-time flags of bfq_ext (bfq_ext.cpp:105-129, 969-1031). */
+typedef struct {
+    int32_t K;          /* -k  minimum LCP inside a cluster            (default 16)   */
+    int32_t m;          /* -m  minimum cluster length                  (default 2; the driver passes 5) */
+    int32_t qthr;       /* -t  quality threshold for trusted bases     (default 20)   */
+    int32_t max_len;    /* -l  maximum read length, <= 255             (driver passes 250) */
+    float   fthr;       /* -f  percentage threshold for frequent bases (default 40)   */
+    uint8_t eos_byte;   /* -s  end-marker byte: 35 (gsufsort) or 0 (eGap; what the driver passes) */
+    uint8_t default_q;  /* -v  replacement quality, ASCII, used when M=2 (default '>') */
+} bfq_params;
+
+/* The statistics block bfq_ext prints (bfq_ext.cpp:1113-1128). */
+typedef struct {
+    uint64_t clusters;      /* "is the total number of clusters"      */
+    uint64_t discarded;     /* "Discarded"                             */
+    uint64_t ambiguous;     /* "Ambiguous discarded"                   */
+    uint64_t processed;     /* "Processed"                             */
+    uint64_t bases_inside;  /* "bases fall inside clusters"            */
+    uint64_t qs_smoothed;   /* "qualities have been modified"          */
+    uint64_t modified;      /* "bases have been modified"              */
+    uint64_t nreads;        /* numSeq                                  */
+    uint64_t n;             /* BWT length                              */
+} bfq_stats;
+
+int         bfq_mode_M(void);
+int         bfq_mode_B(void);
+const char *bfq_last_error(void);
+void        bfq_params_default(bfq_params *p);          /* reference defaults, eos 35, max_len 250 */
+
+int  bfq_ctx_create(bfq_ctx **out, int device);
+void bfq_ctx_destroy(bfq_ctx *ctx);
+/* Tunables (tests use them to force rarely-taken paths).  Unknown key -> BFQ_EINVAL.
+ *   "initial_k"   symbols in the initial radix key (1..21, 0 = auto)
+ *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
+ *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)      */
+int  bfq_ctx_set_option(bfq_ctx *ctx, const char *key, int64_t value);
+
+/* ---- host-buffer entry points (what the tools and the e2e benchmark call) ------------- */
+
+/* Part A.  bases/quals: the reads concatenated without separators, off[nreads+1] their
+ * boundaries.  Writes N = off[nreads] + nreads bytes to each of bwt, qs, lcp. */
+int bfq_build_ebwt(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const uint64_t *off,
+                   uint64_t nreads, uint8_t eos_byte, uint8_t *bwt, uint8_t *qs, uint8_t *lcp);
+
+/* Parts B+C.  out_bases/out_quals need n bytes of capacity, out_off off_capacity entries
+ * (>= nreads+1, nreads = number of EOS bytes in bwt).  Reads come back in input order. */
+int bfq_smooth_rebuild(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, const uint8_t *lcp,
+                       uint64_t n, const bfq_params *params,
+                       uint8_t *out_bases, uint8_t *out_quals, uint64_t *out_off,
+                       uint64_t off_capacity, bfq_stats *stats);
+
+/* Parts A+B+C fused.  bwt/qs/lcp may be NULL (then they are not copied back).
+ * out_bases/out_quals: off[nreads] bytes (read lengths are unchanged; offsets == off). */
+int bfq_pipeline(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const uint64_t *off,
+                 uint64_t nreads, const bfq_params *params,
+                 uint8_t *bwt, uint8_t *qs, uint8_t *lcp,
+                 uint8_t *out_bases, uint8_t *out_quals, bfq_stats *stats);
+
+/* ---- device-buffer entry point (inputs already resident in HBM; what `value` times) --- */
+/* All pointers are device pointers on ctx's device, except stats (host).  d_bwt/d_qs/d_lcp
+ * may be NULL.  total_bases == off[nreads].  Runs on ctx's stream and synchronises it. */
+int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals,
+                     const uint64_t *d_off, uint64_t nreads, uint64_t total_bases,
+                     const bfq_params *params, uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp,
+                     uint8_t *d_out_bases, uint8_t *d_out_quals, bfq_stats *stats);
+
+/* ---- introspection ---------------------------------------------------------------------- */
+/* After a smooth_rebuild/pipeline call: the per-row state the reference keeps in
+ * tmp/bwt_qs_<p>.aux and BWT_MOD/rbv (bfq_ext.cpp:555-556, 810-811), in global row order.
+ * qs_out = stored qualities (after smoothing; after binning too when B=1);
+ * obwt_out = output bases (bwt with noise-reduced rows replaced).  Host buffers of n bytes. */
+int bfq_export_rows(bfq_ctx *ctx, uint8_t *qs_out, uint8_t *obwt_out);
+
+/* Profile counters, filled when option "profile"=1.  Classes: "radix_pass", "radix_hist",
+ * "pack", "keys", "regroup", "gather", "hist", "rank", "cluster", "cluster_long", "rule11",
+ * "walk", "assemble".  Returns accumulated device ms, launch count and algorithmic bytes
+ * since bfq_prof_reset.  Unknown class -> BFQ_EINVAL. */
+int  bfq_prof_get(bfq_ctx *ctx, const char *klass, double *ms, uint64_t *launches, uint64_t *bytes);
+void bfq_prof_reset(bfq_ctx *ctx);
+/* number of kernel launches issued by this ctx since creation (bench.py's gpu_launches) */
+uint64_t bfq_launch_count(bfq_ctx *ctx);
+
+/* ---- test hooks (exercise one kernel family through the same ABI) ---------------------- */
+/* Stable LSD radix sort of (key, value) pairs on the low `bits` bits; host buffers, in place. */
+int bfq_debug_sort_pairs(bfq_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t n, int bits);
+/* Suffix array (text positions, terminators included) of the collection; sa has N entries. */
+int bfq_debug_suffix_array(bfq_ctx *ctx, const uint8_t *bases, const uint64_t *off,
+                           uint64_t nreads, uint32_t *sa);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BFQ_GPU_H */

@@ -1,0 +1,189 @@
+"""GPU parity: the CUDA path through the C ABI vs the oracle / golden vectors (bit-exact)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from bfqzip_b200 import lib, synth
+
+pytestmark = pytest.mark.gpu
+
+MODES = [(M, B) for M in range(4) for B in range(2)]
+STAT_KEYS = ["clusters", "discarded", "ambiguous", "processed", "bases_inside", "qs_smoothed", "modified"]
+GOLD = sorted(glob.glob(os.path.join(H.GOLDEN, "*.npz")))
+GIDS = [os.path.basename(p)[:-4] for p in GOLD]
+
+_ctx = {}
+
+
+def ctx(M=2, B=0):
+    if (M, B) not in _ctx:
+        _ctx[(M, B)] = lib.BfqGpu(M, B, 0)
+    return _ctx[(M, B)]
+
+
+# ---------------------------------------------------------------- radix sort
+@pytest.mark.parametrize("n,bits", [(1, 8), (5, 3), (255, 8), (4096, 16), (4097, 13), (100000, 48),
+                                    (1 << 20, 54), (3000001, 64), (70000, 1)])
+def test_radix_sort_pairs(n, bits):
+    rng = np.random.default_rng(n + bits)
+    keys = rng.integers(0, 1 << 63, size=n, dtype=np.uint64)
+    if bits < 64:
+        keys &= np.uint64((1 << bits) - 1)
+    if n > 1000:            # many duplicates: stability matters
+        keys[: n // 2] = keys[rng.integers(0, 50, size=n // 2)]
+    vals = np.arange(n, dtype=np.uint32)
+    k2, v2 = ctx().debug_sort_pairs(keys, vals, bits)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(k2, keys[order])
+    assert np.array_equal(v2, vals[order])
+
+
+def test_radix_sort_ignores_high_bits():
+    rng = np.random.default_rng(5)
+    keys = rng.integers(0, 1 << 40, size=50000, dtype=np.uint64)
+    vals = np.arange(50000, dtype=np.uint32)
+    k2, v2 = ctx().debug_sort_pairs(keys, vals, 16)
+    order = np.argsort(keys & np.uint64(0xFFFF), kind="stable")
+    assert np.array_equal(v2, vals[order])
+
+
+# ---------------------------------------------------------------- part A
+@pytest.mark.parametrize("path", GOLD, ids=GIDS)
+def test_part_a_golden(path):
+    g = np.load(path)
+    bwt, qs, lcp = ctx().build_ebwt(g["bases"], g["quals"], g["off"], 35)
+    assert np.array_equal(bwt, g["bwt"])
+    assert np.array_equal(qs, g["qs"])
+    assert np.array_equal(lcp, g["lcp"])
+
+
+@pytest.mark.parametrize("k", [1, 3, 7, 10, 16, 21])
+def test_part_a_initial_k(k):
+    g = np.load(os.path.join(H.GOLDEN, "syn_var_dup.npz"))
+    c = ctx()
+    c.set_option("initial_k", k)
+    try:
+        bwt, qs, lcp = c.build_ebwt(g["bases"], g["quals"], g["off"], 35)
+    finally:
+        c.set_option("initial_k", 0)
+    assert np.array_equal(bwt, g["bwt"]) and np.array_equal(qs, g["qs"]) and np.array_equal(lcp, g["lcp"])
+
+
+@pytest.mark.parametrize("eos", [0, 35])
+def test_part_a_eos_byte(eos):
+    """eGap writes 0, gsufsort '#': identical files otherwise."""
+    g = np.load(os.path.join(H.GOLDEN, "example.npz"))
+    bwt, qs, lcp = ctx().build_ebwt(g["bases"], g["quals"], g["off"], eos)
+    ref = g["bwt"].copy(); ref[g["bwt"] == 35] = eos
+    rq = g["qs"].copy(); rq[g["bwt"] == 35] = eos
+    assert np.array_equal(bwt, ref) and np.array_equal(qs, rq) and np.array_equal(lcp, g["lcp"])
+
+
+@pytest.mark.parametrize("seed,nreads,L,var", [(1, 20000, 100, False), (2, 30000, 150, True), (3, 5000, 250, True),
+                                               (4, 1, 50, False), (5, 2, 1, False), (6, 60000, 36, False)])
+def test_part_a_vs_oracle(seed, nreads, L, var):
+    bases, quals, off = synth.make_reads(nreads, L, seed, var_len=var)
+    bwt, qs, lcp = ctx().build_ebwt(bases, quals, off, 35)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+
+
+def test_part_a_identical_reads():
+    """All reads equal: every group is resolved only by the per-read end-markers."""
+    one = np.frombuffer(b"ACGTNACGTTTGACA" * 6, dtype=np.uint8)
+    R = 700
+    bases = np.tile(one, R); quals = np.full(bases.size, 70, np.uint8)
+    off = np.arange(R + 1, dtype=np.uint64) * np.uint64(one.size)
+    bwt, qs, lcp = ctx().build_ebwt(bases, quals, off, 35)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+
+
+# ---------------------------------------------------------------- parts B + C
+@pytest.mark.parametrize("mode", MODES, ids=[f"M{m}B{b}" for m, b in MODES])
+@pytest.mark.parametrize("path", GOLD, ids=GIDS)
+def test_part_bc_golden(path, mode):
+    M, B = mode
+    g = np.load(path)
+    P = lib.default_params(eos=35)
+    ob, oq, off, st = ctx(M, B).smooth_rebuild(g["bwt"], g["qs"], g["lcp"], P)
+    assert np.array_equal(off, g["off"])
+    assert np.array_equal(ob, g[f"out_bases_M{M}_B{B}"])
+    assert np.array_equal(oq, g[f"out_quals_M{M}_B{B}"])
+    assert [st[k] for k in STAT_KEYS] == [int(x) for x in g[f"stats_M{M}_B{B}"]]
+
+
+@pytest.mark.parametrize("mode", [(0, 0), (1, 0), (2, 0), (3, 0)], ids=lambda m: f"M{m[0]}")
+def test_smoothed_rows_match_oracle(mode):
+    """The per-row state (smoothed qualities, modified bases) before reconstruction."""
+    M, B = mode
+    g = np.load(os.path.join(H.GOLDEN, "syn_fixed.npz"))
+    c = ctx(M, B)
+    c.smooth_rebuild(g["bwt"], g["qs"], g["lcp"], lib.default_params(eos=35))
+    q, b = c.export_rows(len(g["bwt"]))
+    sq, ob, st, err = H.oracle_smooth(g["bwt"], g["qs"], g["lcp"], H.make_params(M=M, B=B))
+    rows = g["bwt"] != 35
+    assert np.array_equal(q[rows], sq[rows])
+    assert np.array_equal(b, ob)
+
+
+@pytest.mark.parametrize("long_len", [4, 16, 64])
+@pytest.mark.parametrize("mode", [(0, 0), (1, 1), (2, 0), (3, 0)], ids=lambda m: f"M{m[0]}B{m[1]}")
+def test_long_cluster_path(mode, long_len):
+    """Force the block-per-cluster kernel and clusters that straddle tiles."""
+    M, B = mode
+    bases, quals, off = synth.make_reads(9000, 80, 77, coverage=200.0, err=0.03)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    c = ctx(M, B)
+    c.set_option("long_cluster", long_len)
+    try:
+        ob, oq, o2, st = c.smooth_rebuild(rb, rq, rl, lib.default_params(eos=35))
+    finally:
+        c.set_option("long_cluster", 1024)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B))
+    assert np.array_equal(o2, eoff) and np.array_equal(ob, eb) and np.array_equal(oq, eq)
+    assert all(st[k] == est[k] for k in STAT_KEYS)
+
+
+@pytest.mark.parametrize("K,m", [(16, 2), (8, 5), (30, 3), (1, 5), (200, 5)])
+def test_params_K_m(K, m):
+    g = np.load(os.path.join(H.GOLDEN, "syn_var_dup.npz"))
+    P = lib.default_params(eos=35, K=K, m=m)
+    ob, oq, off, st = ctx(1, 0).smooth_rebuild(g["bwt"], g["qs"], g["lcp"], P)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(g["bwt"], g["qs"], g["lcp"], H.make_params(M=1, B=0, K=K, m=m))
+    assert np.array_equal(ob, eb) and np.array_equal(oq, eq) and np.array_equal(off, eoff)
+    assert all(st[k] == est[k] for k in STAT_KEYS)
+
+
+# ---------------------------------------------------------------- fused pipeline
+@pytest.mark.parametrize("mode", MODES, ids=[f"M{m}B{b}" for m, b in MODES])
+def test_pipeline_vs_oracle(mode):
+    M, B = mode
+    bases, quals, off = synth.make_reads(25000, 100, 500 + M * 2 + B)
+    (bwt, qs, lcp), (ob, oq), st = ctx(M, B).pipeline(bases, quals, off, lib.default_params(eos=0))
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 0)
+    assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B, eos=0))
+    assert np.array_equal(ob, eb) and np.array_equal(oq, eq)
+    assert all(st[k] == est[k] for k in STAT_KEYS)
+
+
+def test_pipeline_roundtrip_1M():
+    """BASELINE config 2 size (1M x 100 bp, M=2): size-independent properties at full size:
+    bases may only change where the oracle rule allows (counted), qualities only inside clusters,
+    read lengths are preserved, the eBWT is a permutation of the input symbols."""
+    bases, quals, off = synth.make_reads(1_000_000, 100, 1001)
+    (bwt, qs, lcp), (ob, oq), st = ctx(2, 0).pipeline(bases, quals, off, lib.default_params(eos=0))
+    n = len(bwt)
+    assert st["nreads"] == 1_000_000 and st["n"] == n
+    assert np.array_equal(np.bincount(bwt, minlength=256)[1:], np.bincount(bases, minlength=256)[1:])
+    assert int((bwt == 0).sum()) == 1_000_000
+    assert np.array_equal(np.sort(qs[bwt != 0]), np.sort(quals))
+    assert int((ob != bases).sum()) == st["modified"]
+    changed = int((oq != quals).sum())
+    assert changed <= st["qs_smoothed"]
+    assert set(np.unique(oq[oq != quals]).tolist()) <= {ord(">")}
+    assert lcp[0] == 0 and int(lcp.max()) <= 100
