@@ -426,7 +426,7 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
             if (i < tile_end) { c = s_code[i - t0]; q = s_q[i - t0]; }
             else { c = s_lut[bwt[i]]; q = qs[i]; }
             if (c) {
-                fpack += 1ull << (12 * c);
+                fpack += 1ull << (12 * (c - 1));
                 acc.base_num++;
                 if ((int)q >= g_sc.qthr + 33) acc.hiq |= 1u << c;
 #if BFQ_M == 0
@@ -439,7 +439,8 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
             }
         }
 #pragma unroll
-        for (int c = 0; c < 6; c++) acc.freq[c] = (uint32_t)(fpack >> (12 * c)) & 0xFFFu;
+        for (int c = 1; c < 6; c++) acc.freq[c] = (uint32_t)(fpack >> (12 * (c - 1))) & 0xFFFu;
+        acc.freq[0] = 0;
         Decision d = decide(len, acc, st);
         if (d.act == ACT_RULE11) {
             uint32_t k = atomicAdd(L.r11_count, 1u);
