@@ -73,6 +73,7 @@ struct bfq_ctx {
     int device = 0;
     int num_sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t own_stream = nullptr;
     bfq::Arena arena;
     // host pinned scratch for small read-backs
     uint64_t *h_small = nullptr;      // 4 KiB pinned

@@ -154,7 +154,8 @@ int bfq_ctx_create(bfq_ctx **out, int device)
             return BFQ_ENODEVICE;
         }
         c->num_sms = prop.multiProcessorCount;
-        BFQ_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        BFQ_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+        c->stream = c->own_stream;
         BFQ_CUDA(cudaMallocHost(&c->h_small, 4096));
         BFQ_CUDA(cudaMalloc(&c->d_small, 4096));
     } catch (Error &er) {
@@ -175,7 +176,7 @@ void bfq_ctx_destroy(bfq_ctx *c)
     c->arena.destroy();
     if (c->h_small) cudaFreeHost(c->h_small);
     if (c->d_small) cudaFree(c->d_small);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }
 
@@ -187,6 +188,16 @@ int bfq_ctx_set_option(bfq_ctx *c, const char *key, int64_t value)
     else if (k == "long_cluster") { if (value < 4) { set_error("long_cluster must be >= 4"); return BFQ_EINVAL; } c->opt_long_cluster = value; }
     else if (k == "profile") c->opt_profile = value ? 1 : 0;
     else { set_error("unknown option '%s'", key); return BFQ_EINVAL; }
+    return BFQ_OK;
+}
+
+int bfq_ctx_set_stream(bfq_ctx *c, void *cuda_stream)
+{
+    if (!c) { set_error("set_stream: null context"); return BFQ_EINVAL; }
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    prof_collect(c);
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
     return BFQ_OK;
 }
 

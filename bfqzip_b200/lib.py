@@ -103,6 +103,9 @@ class BfqGpu:
     def set_option(self, key: str, value: int):
         self._chk(self.lib.bfq_ctx_set_option(self.h, key.encode(), C.c_int64(value)))
 
+    def set_stream(self, cuda_stream_ptr: int | None):
+        self._chk(self.lib.bfq_ctx_set_stream(self.h, C.c_void_p(cuda_stream_ptr or 0)))
+
     def launch_count(self) -> int:
         return int(self.lib.bfq_launch_count(self.h))
 

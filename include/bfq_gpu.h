@@ -82,6 +82,9 @@ void bfq_ctx_destroy(bfq_ctx *ctx);
  *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
  *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)      */
 int  bfq_ctx_set_option(bfq_ctx *ctx, const char *key, int64_t value);
+/* Run on a caller-owned CUDA stream (a cudaStream_t cast to void*) instead of the context's own,
+ * so that the caller's events bracket the library's kernels.  NULL restores the own stream. */
+int  bfq_ctx_set_stream(bfq_ctx *ctx, void *cuda_stream);
 
 /* ---- host-buffer entry points (what the tools and the e2e benchmark call) ------------- */
 
