@@ -1,0 +1,112 @@
+// step1_main.cpp -- drop-in for the step-1 tool of the BFQzip pipelines: FASTQ -> OUT.bwt,
+// OUT.bwt.qs, OUT.<b>.lcp, computed on the GPU through the C ABI (include/bfq_gpu.h).
+//
+// One binary, two command-line spellings, chosen by the name it is invoked under:
+//   eGap      IN.fastq --em --mem <MB> --qs -o OUT --lcp --lbytes 1     (BFQzip_ext.py:165-183;
+//             options of external/egap/eGap:55-80).  End-marker byte 0, like eGap writes.
+//   gsufsort  IN.fastq --bwt --qs --lcp 1 -o OUT                        (BFQzip.py:184; options
+//             of external/gsufsort/main.c:113-146).  End-marker byte '#' (lib/utils.h:57-63).
+// `--mem 0` is accepted (the driver passes it for inputs < 1 MiB).  Options that ask
+// for structures outside this path (SA, DA, --rev, --bwt input ...) are refused with a non-zero
+// exit status: the driver maps any non-zero status to failure (BFQzip_ext.py:310-318).
+#include "fastq_io.hpp"
+#include "../include/bfq_gpu.h"
+#include <stdlib.h>
+#include <chrono>
+
+static const char *base_name(const char *p)
+{
+    const char *s = strrchr(p, '/');
+    return s ? s + 1 : p;
+}
+
+static void die(const std::string &m)
+{
+    fprintf(stderr, "Error: %s\n", m.c_str());
+    exit(EXIT_FAILURE);
+}
+
+int main(int argc, char **argv)
+{
+    const bool gsuf_name = strstr(base_name(argv[0]), "gsufsort") != nullptr;
+    bool gsuf = gsuf_name;
+    std::vector<std::string> inputs;
+    std::string out;
+    bool want_lcp = false, want_qs = false, want_bwt = false;
+    int lbytes = -1, device = 0, verbose = 0;
+    for (int i = 1; i < argc; i++) {
+        std::string a = argv[i];
+        auto next_int = [&](int &dst) {
+            if (i + 1 < argc && argv[i + 1][0] != '-') { dst = atoi(argv[++i]); return true; }
+            return false;
+        };
+        if (a == "--style=egap") gsuf = false;
+        else if (a == "--style=gsufsort") gsuf = true;
+        else if (a == "-o" || a == "--out" || a == "--output") { if (++i >= argc) die("-o needs a value"); out = argv[i]; }
+        else if (a == "--qs" || (a == "-q" && !gsuf) || (a == "-Q" && gsuf)) want_qs = true;
+        else if (gsuf && (a == "-q" || a == "-l")) {}         // gsufsort: -q = FASTQ input, -l = light (main.c:135-137)
+        else if (a == "--bwt" || a == "-B") { want_bwt = true; if (!gsuf) die("eGap --bwt (inputs are BWT files) is outside this path"); }
+        else if (a == "--lcp" || (a == "-l" && !gsuf) || (a == "-L" && gsuf)) {
+            want_lcp = true;
+            if (gsuf) next_int(lbytes);                        // gsufsort: optional byte count (main.c:183-185)
+        }
+        else if (a == "--lbytes") { if (!next_int(lbytes)) die("--lbytes needs a value"); }
+        else if (a == "--mem" || a == "-m") { int mem; if (!next_int(mem)) die("--mem needs a value"); (void)mem; }
+        else if (a == "--em" || a == "--se" || a == "--im" || a == "--fastq" || a == "--build" || a == "--time") {}
+        else if (a == "-v" || a == "--verbose") verbose++;
+        else if (a == "--device") { if (!next_int(device)) die("--device needs a value"); }
+        else if (a == "-h" || a == "--help") {
+            printf("%s IN.fastq %s -o OUT\n  GPU drop-in (sm_100a): writes OUT.bwt, OUT.bwt.qs, OUT.<b>.lcp\n", argv[0],
+                   gsuf ? "--bwt --qs --lcp 1" : "--em --mem M --qs --lcp --lbytes 1");
+            return 0;
+        }
+        else if (a.size() > 1 && a[0] == '-') die("option " + a + " is outside the eBWT/QS/LCP path this tool replaces");
+        else inputs.push_back(a);
+    }
+    if (inputs.empty()) die("no input file");
+    if (gsuf && inputs.size() != 1) die("gsufsort takes exactly one input (main.c:232-235)");
+    if (out.empty()) out = gsuf ? base_name(inputs[0].c_str()) : inputs[0];
+    if (lbytes < 0) lbytes = gsuf ? 4 : 2;                     // tool defaults (main.c:92, eGap:66)
+    if (lbytes != 1 && lbytes != 2 && lbytes != 4) die("LCP entries of 1, 2 or 4 bytes are supported");
+    (void)want_bwt;
+
+    try {
+        auto t0 = std::chrono::steady_clock::now();
+        bfqio::Reads R;
+        for (auto &p : inputs) {                                // eGap concatenates its inputs into one collection
+            bfqio::MappedFile f(p);
+            bfqio::load_fastq(f, R);
+        }
+        const uint64_t nreads = R.nreads(), N = R.bases.size() + nreads;
+        const uint8_t eos = gsuf ? (uint8_t)'#' : (uint8_t)0;
+        std::vector<uint8_t> bwt(N), qs(N), lcp(N);
+        bfq_ctx *ctx = nullptr;
+        if (bfq_ctx_create(&ctx, device) != BFQ_OK) die(bfq_last_error());
+        auto t1 = std::chrono::steady_clock::now();
+        int rc = bfq_build_ebwt(ctx, R.bases.data(), R.quals.data(), R.off.data(), nreads, eos, bwt.data(), qs.data(), lcp.data());
+        if (rc != BFQ_OK) die(bfq_last_error());
+        auto t2 = std::chrono::steady_clock::now();
+        bfq_ctx_destroy(ctx);
+        bfqio::write_all(out + ".bwt", bwt.data(), N);
+        if (want_qs) bfqio::write_all(out + ".bwt.qs", qs.data(), N);
+        if (want_lcp) {
+            // LCP values fit one byte (reads <= 250 bp); wider entries are zero-extended, little-endian,
+            // as both tools write the low lbytes of an int (main.c:891-895)
+            const std::string name = out + "." + std::to_string(lbytes) + ".lcp";
+            if (lbytes == 1) bfqio::write_all(name, lcp.data(), N);
+            else {
+                std::vector<uint8_t> wide(N * (size_t)lbytes, 0);
+                for (uint64_t i = 0; i < N; i++) wide[i * lbytes] = lcp[i];
+                bfqio::write_all(name, wide.data(), wide.size());
+            }
+        }
+        auto t3 = std::chrono::steady_clock::now();
+        auto sec = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
+        printf("%s (GPU): %llu reads, %llu symbols; load %.3f s, eBWT+QS+LCP %.3f s, write %.3f s\n", gsuf ? "gsufsort" : "eGap",
+               (unsigned long long)nreads, (unsigned long long)N, sec(t0, t1), sec(t1, t2), sec(t2, t3));
+        (void)verbose;
+    } catch (std::exception &e) {
+        die(e.what());
+    }
+    return 0;
+}
