@@ -202,7 +202,7 @@ def gpu_arm(args):
     sampler.stop_evt.set(); sampler.join()
     ms = e0.elapsed_time(e1)
     launches = g.launch_count() - l0
-    prof = {k: g.prof_get(k) for k in ("radix_pass", "radix_hist", "pack", "keys", "regroup", "gather", "hist", "rank",
+    prof = {k: g.prof_get(k) for k in ("radix_pass", "radix_hist", "pack", "keys", "group", "defer", "hist", "rank",
                                         "cluster", "cluster_long", "rule11", "walk", "assemble")}
 
     # ---- e2e: host pinned buffers through bfq_pipeline (H2D + D2H inside the timing)

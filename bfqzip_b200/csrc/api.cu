@@ -98,7 +98,7 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     if (!d_lcp) d_lcp = arena_alloc<uint8_t>(c, N + 64);
     {
         Arena::Mark mk = c->arena.mark();
-        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, P->eos_byte, d_bwt, d_qs, d_lcp, nullptr);
+        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, P->eos_byte, d_bwt, d_qs, d_lcp, nullptr);
         c->arena.release(mk);        // sort scratch is dead (stream-ordered) once the gather is queued
     }
     SmoothResult S;
@@ -123,14 +123,17 @@ using namespace bfq;
 #define API_END   return BFQ_OK; } catch (bfq::Error &e__) { if (ctx) cudaStreamSynchronize(ctx->stream); cudaGetLastError(); return e__.code; } \
                   catch (std::exception &ex__) { bfq::set_error("exception: %s", ex__.what()); return BFQ_ENOMEM; }
 
-static uint64_t host_check_off(const uint64_t *off, uint64_t nreads)
+static uint64_t host_check_off(const uint64_t *off, uint64_t nreads, uint64_t *max_len = nullptr)
 {
+    uint64_t mx = 0;
     if (off[0] != 0) BFQ_FAIL(BFQ_EINVAL, "off[0] must be 0");
     for (uint64_t g = 0; g < nreads; g++) {
         if (off[g + 1] < off[g]) BFQ_FAIL(BFQ_EINVAL, "read offsets are not non-decreasing (read %llu)", (unsigned long long)g);
         if (off[g + 1] == off[g])
             BFQ_FAIL(BFQ_EINVAL, "read %llu is empty: the reference drops empty reads (external/gsufsort/lib/utils.c:229-236); remove them first", (unsigned long long)g);
+        mx = std::max(mx, off[g + 1] - off[g]);
     }
+    if (max_len) *max_len = mx;
     return off[nreads];
 }
 
@@ -148,12 +151,13 @@ int bfq_build_ebwt(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, con
 {
     API_BEGIN
     if (!off || !bwt || !qs || !lcp || (nreads && (!bases || !quals))) BFQ_FAIL(BFQ_EINVAL, "bfq_build_ebwt: null pointer");
-    const uint64_t total = host_check_off(off, nreads), N = total + nreads;
+    uint64_t mxl = 0;
+    const uint64_t total = host_check_off(off, nreads, &mxl), N = total + nreads;
     if (N == 0) return BFQ_OK;
     uint8_t *d_b = to_device(ctx, bases, total), *d_q = to_device(ctx, quals, total);
     uint64_t *d_o = to_device(ctx, off, nreads + 1);
     uint8_t *d_bwt = arena_alloc<uint8_t>(ctx, N + 64), *d_qs = arena_alloc<uint8_t>(ctx, N + 64), *d_lcp = arena_alloc<uint8_t>(ctx, N + 64);
-    build_ebwt_dev(ctx, d_b, d_q, d_o, nreads, total, eos_byte, d_bwt, d_qs, d_lcp, nullptr);
+    build_ebwt_dev(ctx, d_b, d_q, d_o, nreads, total, mxl, eos_byte, d_bwt, d_qs, d_lcp, nullptr);
     BFQ_CUDA(cudaMemcpyAsync(bwt, d_bwt, N, cudaMemcpyDeviceToHost, ctx->stream));
     BFQ_CUDA(cudaMemcpyAsync(qs, d_qs, N, cudaMemcpyDeviceToHost, ctx->stream));
     BFQ_CUDA(cudaMemcpyAsync(lcp, d_lcp, N, cudaMemcpyDeviceToHost, ctx->stream));
@@ -259,12 +263,13 @@ int bfq_debug_suffix_array(bfq_ctx *ctx, const uint8_t *bases, const uint64_t *o
 {
     API_BEGIN
     if (!off || !sa || (nreads && !bases)) BFQ_FAIL(BFQ_EINVAL, "null pointer");
-    const uint64_t total = host_check_off(off, nreads), N = total + nreads;
+    uint64_t mxl = 0;
+    const uint64_t total = host_check_off(off, nreads, &mxl), N = total + nreads;
     if (N == 0) return BFQ_OK;
     uint8_t *d_b = to_device(ctx, bases, total);
     uint64_t *d_o = to_device(ctx, off, nreads + 1);
     uint32_t *d_sa = arena_alloc<uint32_t>(ctx, N + 16);
-    build_ebwt_dev(ctx, d_b, d_b, d_o, nreads, total, '#', nullptr, nullptr, nullptr, d_sa);
+    build_ebwt_dev(ctx, d_b, d_b, d_o, nreads, total, mxl, '#', nullptr, nullptr, nullptr, d_sa);
     BFQ_CUDA(cudaMemcpyAsync(sa, d_sa, N * 4, cudaMemcpyDeviceToHost, ctx->stream));
     BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
     API_END

@@ -41,11 +41,11 @@ struct Error { int code; };   // thrown inside the library, caught at the C ABI
 
 // ---------------------------------------------------------------- profiling classes
 enum ProfClass {
-    PC_RADIX_PASS = 0, PC_RADIX_HIST, PC_PACK, PC_KEYS, PC_REGROUP, PC_GATHER, PC_HIST, PC_RANK,
+    PC_RADIX_PASS = 0, PC_RADIX_HIST, PC_PACK, PC_KEYS, PC_GROUP, PC_DEFER, PC_HIST, PC_RANK,
     PC_CLUSTER, PC_CLUSTER_LONG, PC_RULE11, PC_WALK, PC_ASSEMBLE, PC_COUNT
 };
 static const char *const kProfNames[PC_COUNT] = {
-    "radix_pass", "radix_hist", "pack", "keys", "regroup", "gather", "hist", "rank",
+    "radix_pass", "radix_hist", "pack", "keys", "group", "defer", "hist", "rank",
     "cluster", "cluster_long", "rule11", "walk", "assemble"};
 
 struct ProfEntry {
@@ -81,6 +81,7 @@ struct bfq_ctx {
     // options
     int opt_initial_k = 0;
     int64_t opt_long_cluster = 1024;
+    int64_t opt_group_cap = 1 << 20;
     int opt_profile = 0;
     // accounting
     uint64_t launches = 0;
@@ -129,7 +130,7 @@ struct EbwtDev {                 // device results of part A
 
 // sufsort.cu
 void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
-                    uint64_t nreads, uint64_t total_bases, uint8_t eos_byte,
+                    uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos_byte,
                     uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out);
 // smooth.cu
 struct SmoothResult {

@@ -1,5 +1,6 @@
-// sufsort.cu -- part A on the device: generalized suffix sort of a read collection by prefix
-// doubling, then the eBWT / permuted-quality gather and the LCP array.
+// sufsort.cu -- part A on the device: generalized suffix sort of a read collection by MSD
+// radix (k symbols, stable LSD) + in-shared-memory string sort, with the eBWT / permuted-quality /
+// LCP rows produced by the same kernel.
 //
 // Replaces: external/gsufsort/lib/utils.c:193-249 (cat_all),
 // external/gsufsort/external/gsacak.c:1648-1930, 2503-2518 (gSACA-K + LCP) and
@@ -10,14 +11,14 @@
 // (utils.c:229-246).  Every terminator is a distinct symbol ordered by read index
 // (gsacak.c:113-133), so after sorting on the first k symbols (cut at the terminator) a key
 // that contains a terminator is unique and is ranked by text position -- a stable sort from
-// position order gives that for free.  Unresolved groups never contain a terminator in
-// their first h symbols, hence ISA[p+h] is always a position of the same read.
+// position order gives that for free.  Groups of equal terminator-free keys are finished by
+// sorting the rest of their suffixes inside shared memory (group_tile_kernel).
 //
 // Layouts in HBM (N = sum(len+1) rows, N < 2^32):
 //   T3   3-bit codes, big-endian bit stream, 64 symbols per three u64 words (fits L2 for cfg2)
 //   Q    N bytes, quality of position p (EOS byte at terminators)
-//   SA   u32[N] final suffix array (text positions); ISA u32[N] group-head rank of each position
-//   active list (sorted by group): pos u32, slot u32 (global SA index of the list slot), gid u32
+//   key  u64[N] x2, pos u32[N] x2   sort ping-pong: (k-symbol key, text position)
+//   level >= 1 lists (members of groups too large for one tile) reuse the same ping-pong pair
 #include "common.cuh"
 #include <algorithm>
 
@@ -148,188 +149,350 @@ init_keys_kernel(const uint64_t *__restrict__ T3, uint32_t n, int k, K *__restri
     vals[p] = p;
 }
 
-// ============================================================================ regroup
-// After a sort: find the new groups, rank them, retire singletons, compact the rest.
-// One chained scan (three look-back words per tile: max, kept count, kept-head count).
-constexpr int RG_THREADS = 256;
-constexpr int RG_ITEMS = 4;
-constexpr int RG_TILE = RG_THREADS * RG_ITEMS;
+// ============================================================================ group tile kernel
+// After a stable radix sort on a key of `ksym` symbols (cut at the terminator) the list is a
+// sequence of GROUPS (runs of equal keys).  A key that holds a terminator is unique (every
+// terminator is its own symbol, gsacak.c:113-133) and already in read order because the sort is
+// stable from position order, so such rows are final.  Every other group shares depth = depth0 +
+// ksym symbols and is finished here, inside shared memory: the rest of every member's suffix
+// (<= W words of 21 symbols, cut at its terminator) is staged from the packed text, one warp
+// sorts the group with a bitonic network over 16-bit member indices (ties = identical strings ->
+// text position, i.e. read index), and the rows leave the SM complete: SA, bwt, qs and lcp.
+// The LCP of a sorted row is depth + the common prefix of two staged strings; the LCP of a
+// group head comes from the two keys.  This fuses what used to be the prefix-doubling rounds and
+// the eBWT/LCP gather (main.c:848-895) into one pass over the sorted list.
+//
+// A block owns the groups that START in its nominal range of GT_T list slots and stages
+// GT_S = GT_T + GT_E slots; a group that does not end inside the staged window is DEFERRED: its
+// start is appended to a list and the host runs one more level on those groups with the next
+// symbols as key (MSD recursion; at most ceil(max_len / 14) levels, only repeats get there).
+constexpr int GT_THREADS = 256;
+constexpr int GT_T = 1024;
+constexpr int GT_E = 512;
+constexpr int GT_S = GT_T + GT_E;
+constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
+constexpr int GT_GMAX = GT_S / 2;
 
-struct RgState { uint32_t mx, keep, heads; };
+struct GroupTileArgs {
+    const uint32_t *pos;        // list payload: text position
+    uint32_t m;                 // list length
+    int level0;                 // 1: slot == list index, key has no group id
+    int ksym;                   // symbols in this level's key (low 3*ksym bits)
+    int depth0;                 // symbols known equal before this key (0 at level 0)
+    int W;                      // words of 21 symbols to stage per member
+    const uint64_t *T3;
+    const uint8_t *Q;
+    const uint32_t *g_slot;     // level >= 1: SA slot of the first member of list group g
+    const uint32_t *g_off;      // level >= 1: list offset of the first member of list group g
+    uint32_t *SA;               // optional
+    uint8_t *bwt, *qs, *lcp;    // optional (all three or none)
+    uint64_t code2byte;
+    uint8_t eos;
+    uint32_t *defer_count;      // [0] groups deferred, [1] members (filled by defer_len_kernel)
+    uint32_t *defer_start;      // list index of the head of every deferred group
+    uint32_t defer_cap;
+    uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
+};
 
-__device__ __forceinline__ RgState rg_combine(RgState a, RgState b)
+__device__ __forceinline__ uint64_t cut_at_terminator(uint64_t w, bool &terminated)
 {
-    return RgState{max(a.mx, b.mx), a.keep + b.keep, a.heads + b.heads};
+    if (terminated) return 0ull;
+    const int f = leading_nonzero_fields(w);
+    if (f < 21) { terminated = true; return f ? (w & (~0ull << (64 - 3 * f))) : 0ull; }
+    return w;
 }
 
-template <typename K, bool INITIAL>
-__global__ void __launch_bounds__(RG_THREADS)
-regroup_kernel(const K *__restrict__ keys, const uint32_t *__restrict__ pos,
-               const uint32_t *__restrict__ slot_in, uint32_t m,
-               uint32_t *__restrict__ ISA, uint32_t *__restrict__ SA,
-               uint32_t *__restrict__ pos_out, uint32_t *__restrict__ slot_out,
-               uint32_t *__restrict__ gid_out,
-               unsigned long long *__restrict__ status /*[tiles][3]*/,
-               uint32_t *__restrict__ tile_counter, uint32_t *__restrict__ totals /*[2]: kept, groups*/)
+// common prefix (in symbols, terminators not counted) of two staged strings
+__device__ __forceinline__ uint32_t staged_lcp(const uint64_t *s_words, int W, uint32_t a, uint32_t b)
 {
-    __shared__ uint32_t s_tile;
-    __shared__ RgState s_warp[RG_THREADS / 32];
-    __shared__ RgState s_prefix;
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
-    __syncthreads();
-    const uint32_t tile = s_tile;
-    const uint32_t j0 = tile * RG_TILE + tid * RG_ITEMS;
-
-    K key[RG_ITEMS + 2];            // key[0] = predecessor, key[RG_ITEMS+1] = successor
-    uint32_t ps[RG_ITEMS], sl[RG_ITEMS];
-    bool head[RG_ITEMS + 1];
-#pragma unroll
-    for (int i = 0; i < RG_ITEMS + 2; i++) {
-        int64_t j = (int64_t)j0 + i - 1;
-        key[i] = (j >= 0 && j < (int64_t)m) ? keys[j] : (K)0;
-    }
-#pragma unroll
-    for (int i = 0; i < RG_ITEMS; i++) {
-        uint32_t j = j0 + i;
-        ps[i] = j < m ? pos[j] : 0u;
-        sl[i] = INITIAL ? j : (j < m ? slot_in[j] : 0u);
-    }
-#pragma unroll
-    for (int i = 0; i <= RG_ITEMS; i++) {
-        uint32_t j = j0 + i;
-        bool h = (j == 0) || (j >= m) || (key[i + 1] != key[i]);
-        if (INITIAL) h = h || ((key[i + 1] & 7) == 0);     // key holds a terminator: unique
-        head[i] = h;
-    }
-    // local aggregate
-    RgState loc{0, 0, 0};
-    bool keep[RG_ITEMS];
-#pragma unroll
-    for (int i = 0; i < RG_ITEMS; i++) {
-        uint32_t j = j0 + i;
-        bool valid = j < m;
-        keep[i] = valid && !(head[i] && head[i + 1]);
-        if (valid && head[i]) loc.mx = max(loc.mx, sl[i]);
-        loc.keep += keep[i] ? 1u : 0u;
-        loc.heads += (keep[i] && head[i]) ? 1u : 0u;
-    }
-    // block exclusive scan of RgState
-    RgState inc = loc;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        RgState y{__shfl_up_sync(0xffffffffu, inc.mx, o), __shfl_up_sync(0xffffffffu, inc.keep, o),
-                  __shfl_up_sync(0xffffffffu, inc.heads, o)};
-        if (lane >= o) inc = rg_combine(y, inc);
-    }
-    if (lane == 31) s_warp[w] = inc;
-    __syncthreads();
-    RgState wpre{0, 0, 0};
-    for (int i = 0; i < w; i++) wpre = rg_combine(wpre, s_warp[i]);
-    // exclusive for this thread = wpre + (inc of previous lane)
-    RgState prev{__shfl_up_sync(0xffffffffu, inc.mx, 1), __shfl_up_sync(0xffffffffu, inc.keep, 1),
-                 __shfl_up_sync(0xffffffffu, inc.heads, 1)};
-    RgState excl = (lane == 0) ? wpre : rg_combine(wpre, prev);
-
-    // tile aggregate + chained scan (lanes 0..2 of warp 0 each own one word)
-    if (w == 0) {
-        RgState agg{0, 0, 0};
-        for (int i = 0; i < RG_THREADS / 32; i++) agg = rg_combine(agg, s_warp[i]);
-        if (lane < 3) {
-            const unsigned long long FL = 62;
-            unsigned long long mine = lane == 0 ? agg.mx : (lane == 1 ? agg.keep : agg.heads);
-            volatile unsigned long long *st = status;
-            st[(size_t)tile * 3 + lane] = ((unsigned long long)(tile == 0 ? 2 : 1) << FL) | mine;
-            unsigned long long ex = 0;
-            if (tile > 0) {
-                int64_t t = (int64_t)tile - 1;
-                while (true) {
-                    unsigned long long v = st[(size_t)t * 3 + lane];
-                    unsigned f = (unsigned)(v >> FL);
-                    if (f == 0) continue;
-                    unsigned long long val = v & ((1ull << FL) - 1);
-                    ex = (lane == 0) ? (ex > val ? ex : val) : ex + val;
-                    if (f == 2) break;
-                    t--;
-                }
-                unsigned long long incl = (lane == 0) ? (ex > mine ? ex : mine) : ex + mine;
-                st[(size_t)tile * 3 + lane] = (2ull << FL) | incl;
-            }
-            if (lane == 0) s_prefix.mx = (uint32_t)ex;
-            if (lane == 1) s_prefix.keep = (uint32_t)ex;
-            if (lane == 2) s_prefix.heads = (uint32_t)ex;
-            // the last tile publishes the totals
-            if ((uint64_t)(tile + 1) * RG_TILE >= m) {
-                if (lane == 1) totals[0] = (uint32_t)(ex + mine);
-                if (lane == 2) totals[1] = (uint32_t)(ex + mine);
-            }
-        }
-    }
-    __syncthreads();
-    RgState run = rg_combine(s_prefix, excl);
-#pragma unroll
-    for (int i = 0; i < RG_ITEMS; i++) {
-        uint32_t j = j0 + i;
-        if (j >= m) break;
-        if (head[i]) run.mx = max(run.mx, sl[i]);
-        // group-head rank of this suffix (global SA index of the first member of its group)
-        ISA[ps[i]] = run.mx;
-        if (head[i] && head[i + 1]) {
-            SA[sl[i]] = ps[i];                    // singleton: final
-        } else {
-            if (head[i]) run.heads++;
-            pos_out[run.keep] = ps[i];
-            slot_out[run.keep] = sl[i];
-            gid_out[run.keep] = run.heads - 1;
-            run.keep++;
-        }
-    }
-}
-
-// key = (compact group id << nbits) | rank of the suffix h symbols further on
-__global__ void __launch_bounds__(256)
-doubling_keys_kernel(const uint32_t *__restrict__ pos, const uint32_t *__restrict__ gid,
-                     const uint32_t *__restrict__ ISA, uint32_t m, uint32_t h, int nbits,
-                     uint64_t *__restrict__ keys)
-{
-    const uint32_t j = blockIdx.x * 256u + threadIdx.x;
-    if (j >= m) return;
-    const uint32_t p = pos[j];
-    keys[j] = ((uint64_t)gid[j] << nbits) | (uint64_t)ISA[p + h];
-}
-
-// ============================================================================ final gather
-// row i: p = SA[i]; bwt/qs from position p-1 (EOS at a read start); lcp by comparing the
-// packed text of SA[i-1] and SA[i] 21 symbols at a time, stopping at either terminator.
-__global__ void __launch_bounds__(256)
-gather_kernel(const uint32_t *__restrict__ SA, const uint64_t *__restrict__ T3,
-              const uint8_t *__restrict__ Q, uint32_t n, uint8_t eos, uint64_t code2byte_packed,
-              uint8_t *__restrict__ bwt, uint8_t *__restrict__ qs, uint8_t *__restrict__ lcp)
-{
-    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t p = SA[i];
-    uint8_t b = eos, q = eos;
-    if (p > 0) {
-        uint32_t c = sym_code(T3, (uint64_t)p - 1);
-        if (c) { b = (uint8_t)(code2byte_packed >> (8 * c)); q = Q[p - 1]; }
-    }
-    bwt[i] = b;
-    qs[i] = q;
     uint32_t l = 0;
-    if (i > 0) {
-        uint64_t a = SA[i - 1], bb = p;
-        while (true) {
-            uint64_t wa = text_window(T3, a + l), wb = text_window(T3, bb + l);
-            int za = leading_nonzero_fields(wa), zb = leading_nonzero_fields(wb);
-            uint64_t x = wa ^ wb;
-            int fm = x ? (__clzll((long long)x) / 3) : 21;
-            int step = min(fm, min(za, zb));
-            l += step;
-            if (step < 21) break;
+    for (int j = 0; j < W; j++) {
+        const uint64_t wa = s_words[j * GT_S + a], wb = s_words[j * GT_S + b];
+        const uint64_t x = wa ^ wb;
+        const int fm = x ? (__clzll((long long)x) / 3) : 21;
+        const int step = min(fm, min(leading_nonzero_fields(wa), leading_nonzero_fields(wb)));
+        l += step;
+        if (step < 21) break;
+    }
+    return l;
+}
+
+// LCP of the head of a group with the row before it, from the two keys (symbol parts)
+template <typename K>
+__device__ __forceinline__ uint32_t head_lcp(K kprev, K kcur, int ksym)
+{
+    // left-align the ksym fields so that field 0 sits in bits 63..61
+    const uint64_t a = (uint64_t)kprev << (64 - 3 * ksym), b = (uint64_t)kcur << (64 - 3 * ksym);
+    const uint64_t x = a ^ b;
+    const int fm = x ? (__clzll((long long)x) / 3) : ksym;
+    // symbols before the terminator (fields below ksym are zero padding -> count as terminator)
+    const int z = leading_nonzero_fields(b);
+    return (uint32_t)min(min(fm, z), ksym);
+}
+
+template <typename K>
+__global__ void __launch_bounds__(GT_THREADS)
+group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
+{
+    extern __shared__ __align__(16) unsigned char gt_smem[];
+    uint64_t *s_words = reinterpret_cast<uint64_t *>(gt_smem);                      // [W][GT_S]
+    uint32_t *s_pos = reinterpret_cast<uint32_t *>(s_words + (size_t)A.W * GT_S);   // [GT_S]
+    uint32_t *s_head = s_pos + GT_S;                                                // [GT_HW]
+    uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] code | q << 8
+    uint16_t *s_gs = s_prev + GT_S;                                                 // [GT_S] group start or 0xFFFF
+    uint16_t *s_sorted = s_gs + GT_S;                                               // [GT_S] member at sorted row
+    uint16_t *s_idx = s_sorted + GT_S;                                              // [2*GT_S] bitonic scratch
+    uint16_t *s_gstart = s_idx + 2 * GT_S;                                          // [GT_GMAX]
+    uint16_t *s_glen = s_gstart + GT_GMAX;                                          // [GT_GMAX]
+    uint16_t *s_gscr = s_glen + GT_GMAX;                                            // [GT_GMAX]
+    __shared__ uint32_t s_ngroups, s_scrtop, s_next;
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t t0 = blockIdx.x * (uint32_t)GT_T;
+    const uint32_t m = A.m;
+    const int W = A.W, ksym = A.ksym;
+    const int depth = A.depth0 + ksym;
+    const int kshift = 3 * ksym;                          // group id sits above the symbols (level >= 1)
+    if (tid == 0) { s_ngroups = 0; s_scrtop = 0; s_next = 0; }
+
+    // ---- phase 0: head bitmap of the staged window (bit r <=> list slot t0 + r starts a group)
+    for (int base = 0; base < GT_HW * 32; base += GT_THREADS) {
+        const int r = base + tid;
+        const uint64_t j = (uint64_t)t0 + r;
+        bool h = true;                                    // slots past the list end count as heads
+        if (r <= GT_S && j < m && j > 0) {
+            const K kc = keys[j], kp = keys[j - 1];
+            h = (kc != kp) || ((kc & (K)7) == 0);
+        }
+        const uint32_t bits = __ballot_sync(0xffffffffu, h);
+        if (lane == 0 && (r >> 5) < GT_HW) s_head[r >> 5] = bits;
+    }
+    __syncthreads();
+
+    auto is_head = [&](int r) -> bool { return (s_head[r >> 5] >> (r & 31)) & 1u; };
+    auto next_head = [&](int r) -> int {                  // first head > r (exists: sentinel region)
+        int w = (r + 1) >> 5;
+        uint32_t bits = s_head[w] & (0xffffffffu << ((r + 1) & 31));
+        while (!bits) bits = s_head[++w];
+        return (w << 5) + __ffs(bits) - 1;
+    };
+    auto prev_head = [&](int r) -> int {                  // last head <= r, or -1
+        int w = r >> 5;
+        uint32_t bits = s_head[w] & (0xffffffffu >> (31 - (r & 31)));
+        while (!bits) { if (--w < 0) return -1; bits = s_head[w]; }
+        return (w << 5) + 31 - __clz(bits);
+    };
+    auto slot_of = [&](uint32_t j) -> uint32_t {
+        if (A.level0) return j;
+        const uint32_t g = (uint32_t)((uint64_t)keys[j] >> kshift);
+        return A.g_slot[g] + (j - A.g_off[g]);
+    };
+
+    // ---- phase 1: ownership, group list, staging of positions / previous symbol / suffix words
+    for (int r = tid; r < GT_S; r += GT_THREADS) {
+        const uint64_t j = (uint64_t)t0 + r;
+        uint16_t gs16 = 0xFFFF;
+        if (j < m) {
+            const int gs = prev_head(r);
+            if (gs >= 0 && gs < GT_T) {
+                const int ge = next_head(r);
+                const int size = ge - gs;
+                const bool fits = ge <= GT_S && (uint32_t)size <= A.group_cap;
+                if (r == gs) {
+                    // head row: its LCP comes from the keys and is final at this level
+                    if (A.lcp) {
+                        bool write = true; uint32_t l = 0;
+                        if (j == 0) write = A.level0;
+                        else {
+                            const K kc = keys[j], kp = keys[j - 1];
+                            if (!A.level0 && ((uint64_t)kc >> kshift) != ((uint64_t)kp >> kshift)) write = false;   // written one level up
+                            else l = A.depth0 + head_lcp<K>(kp, kc, ksym);
+                        }
+                        if (write) A.lcp[slot_of((uint32_t)j)] = (uint8_t)l;
+                    }
+                    if (size > 1) {
+                        if (fits) {
+                            uint32_t n2 = 2;
+                            while ((int)n2 < size) n2 <<= 1;
+                            const uint32_t g = atomicAdd(&s_ngroups, 1u);
+                            s_gstart[g] = (uint16_t)gs; s_glen[g] = (uint16_t)size;
+                            s_gscr[g] = (uint16_t)atomicAdd(&s_scrtop, n2);
+                        } else {
+                            const uint32_t d = atomicAdd(A.defer_count, 1u);
+                            if (d < A.defer_cap) A.defer_start[d] = (uint32_t)j;
+                        }
+                    }
+                }
+                if (fits) {
+                    gs16 = (uint16_t)gs;
+                    const uint32_t p = A.pos[j];
+                    s_pos[r] = p;
+                    s_sorted[r] = (uint16_t)r;
+                    uint32_t c = 0; uint8_t q = A.eos;
+                    if (A.bwt && p > 0) {
+                        c = sym_code(A.T3, (uint64_t)p - 1);
+                        if (c) q = A.Q[p - 1];
+                    }
+                    s_prev[r] = (uint16_t)(c | ((uint32_t)q << 8));
+                    if (size > 1) {
+                        bool term = false;
+                        for (int w = 0; w < W; w++) {
+                            uint64_t x = term ? 0ull : text_window(A.T3, (uint64_t)p + depth + 21 * w);
+                            s_words[w * GT_S + r] = cut_at_terminator(x, term);
+                        }
+                    }
+                }
+            }
+        }
+        s_gs[r] = gs16;
+    }
+    __syncthreads();
+
+    // ---- phase 2: one warp sorts one group (bitonic over member indices, +inf padding)
+    const uint32_t ngroups = s_ngroups;
+    auto less = [&](uint32_t a, uint32_t b) -> bool {
+        if (a == 0xFFFFu) return false;
+        if (b == 0xFFFFu) return true;
+        for (int w = 0; w < W; w++) {
+            const uint64_t wa = s_words[w * GT_S + a], wb = s_words[w * GT_S + b];
+            if (wa != wb) return wa < wb;
+        }
+        return s_pos[a] < s_pos[b];
+    };
+    while (true) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(&s_next, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        const uint32_t gs = s_gstart[g], len = s_glen[g];
+        uint16_t *idx = s_idx + s_gscr[g];
+        uint32_t n2 = 2;
+        while (n2 < len) n2 <<= 1;
+        for (uint32_t i = lane; i < n2; i += 32) idx[i] = i < len ? (uint16_t)(gs + i) : (uint16_t)0xFFFF;
+        __syncwarp();
+        for (uint32_t k = 2; k <= n2; k <<= 1) {
+            for (uint32_t jj = k >> 1; jj > 0; jj >>= 1) {
+                for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
+                    const uint32_t i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
+                    const uint32_t l = i | jj;
+                    const uint32_t a = idx[i], b = idx[l];
+                    const bool up = (i & k) == 0;
+                    const bool sw = up ? less(b, a) : less(a, b);
+                    if (sw) { idx[i] = (uint16_t)b; idx[l] = (uint16_t)a; }
+                }
+                __syncwarp();
+            }
+        }
+        for (uint32_t i = lane; i < len; i += 32) s_sorted[gs + i] = idx[i];
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- phase 3: finished rows leave the SM in slot order
+    for (int r = tid; r < GT_S; r += GT_THREADS) {
+        const uint32_t gs = s_gs[r];
+        if (gs == 0xFFFFu) continue;
+        const uint32_t j = t0 + r;
+        const uint32_t e = s_sorted[r];
+        const uint32_t slot = slot_of(j);
+        if (A.SA) A.SA[slot] = s_pos[e];
+        if (A.bwt) {
+            const uint32_t pv = s_prev[e];
+            const uint32_t c = pv & 7u;
+            A.bwt[slot] = c ? (uint8_t)(A.code2byte >> (8 * c)) : A.eos;
+            A.qs[slot] = (uint8_t)(pv >> 8);
+            if ((uint32_t)r != gs) A.lcp[slot] = (uint8_t)(depth + staged_lcp(s_words, W, s_sorted[r - 1], e));
         }
     }
-    lcp[i] = (uint8_t)l;      // low byte, as main.c:891-895 writes it
+}
+
+static size_t group_tile_smem(int W)
+{
+    return (size_t)W * GT_S * 8 + (size_t)GT_S * 4 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 3 +
+           (size_t)2 * GT_S * 2 + (size_t)GT_GMAX * 2 * 3;
+}
+
+// ============================================================================ deferred groups
+// key of `s` symbols starting at text position p, cut at the terminator, right-aligned
+__device__ __forceinline__ uint64_t cut_key(const uint64_t *__restrict__ T3, uint64_t p, int s)
+{
+    uint64_t w = text_window(T3, p);
+    const int f = leading_nonzero_fields(w);
+    if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
+    return w >> (64 - 3 * s);
+}
+
+// one warp per deferred group: its length (distance to the next head) and the SA slot of its head
+template <typename K>
+__global__ void __launch_bounds__(256)
+defer_len_kernel(const K *__restrict__ keys, uint32_t m, int level0, int kshift,
+                 const uint32_t *__restrict__ g_slot, const uint32_t *__restrict__ g_off,
+                 const uint32_t *__restrict__ dstart, uint32_t G, uint32_t *__restrict__ dlen,
+                 uint32_t *__restrict__ dslot)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t d = (blockIdx.x * 256u + threadIdx.x) >> 5;
+    if (d >= G) return;
+    const uint32_t start = dstart[d];
+    uint32_t end = m;
+    for (uint64_t base = (uint64_t)start + 1; base < m; base += 32) {
+        const uint64_t j = base + lane;
+        bool h = false;
+        if (j < m) { const K kc = keys[j], kp = keys[j - 1]; h = (kc != kp) || ((kc & (K)7) == 0); }
+        const uint32_t b = __ballot_sync(0xffffffffu, h);
+        if (b) { end = (uint32_t)base + __ffs(b) - 1; break; }
+    }
+    if (lane == 0) {
+        dlen[d] = end - start;
+        uint32_t slot = start;
+        if (!level0) { const uint32_t g = (uint32_t)((uint64_t)keys[start] >> kshift); slot = g_slot[g] + (start - g_off[g]); }
+        dslot[d] = slot;
+    }
+}
+
+// single block: exclusive scan of n counters, total to *total
+__global__ void __launch_bounds__(1024)
+scan_excl_u32_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, uint32_t *__restrict__ total)
+{
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + tid;
+        const uint32_t v = i < n ? in[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) s_warp[w] = x;
+        __syncthreads();
+        uint32_t add = 0;
+        for (int k = 0; k < w; k++) add += s_warp[k];
+        const uint32_t carry = s_carry;
+        if (i < n) out[i] = carry + add + x - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + add + x;
+        __syncthreads();
+    }
+    if (tid == 0) *total = s_carry;
+}
+
+// next-level list: members of deferred group d get key (d << 3s) | next s symbols
+__global__ void __launch_bounds__(256)
+defer_fill_kernel(const uint32_t *__restrict__ pos, const uint32_t *__restrict__ dstart,
+                  const uint32_t *__restrict__ dlen, const uint32_t *__restrict__ doff, uint32_t G,
+                  const uint64_t *__restrict__ T3, int depth, int s, uint64_t *__restrict__ keys_out,
+                  uint32_t *__restrict__ pos_out)
+{
+    for (uint32_t d = blockIdx.x; d < G; d += gridDim.x) {
+        const uint32_t start = dstart[d], len = dlen[d], off = doff[d];
+        for (uint32_t i = threadIdx.x; i < len; i += 256) {
+            const uint32_t p = pos[start + i];
+            keys_out[off + i] = ((uint64_t)d << (3 * s)) | cut_key(T3, (uint64_t)p + depth, s);
+            pos_out[off + i] = p;
+        }
+    }
 }
 
 // ============================================================================ host driver
@@ -355,9 +518,19 @@ Alphabet alphabet_from_hist(const uint64_t hist[256], uint8_t eos, bool eos_may_
     return A;
 }
 
+template <typename K>
+static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgs &A)
+{
+    const size_t smem = group_tile_smem(A.W);
+    BFQ_CUDA(cudaFuncSetAttribute(group_tile_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope ps(c, PC_GROUP, (uint64_t)A.m * (sizeof(K) + 4 + 3 + 8 * (uint64_t)A.W));
+    group_tile_kernel<K><<<div_up(A.m, GT_T), GT_THREADS, smem, c->stream>>>(keys, A);
+    BFQ_CUDA(cudaGetLastError());
+}
+
 void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
-                    uint64_t nreads, uint64_t total_bases, uint8_t eos, uint8_t *d_bwt, uint8_t *d_qs,
-                    uint8_t *d_lcp, uint32_t *d_sa_out)
+                    uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
+                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out)
 {
     const uint64_t N = total_bases + nreads;
     if (N == 0) return;
@@ -376,18 +549,16 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     for (int k = 0; k < 8; k++) c2b |= (uint64_t)A.code2byte[k] << (8 * k);
 
     // ---- buffers
-    const uint64_t ngroups = (N + 64 + 63) / 64;            // padded so windows past the end read zeros
+    const uint64_t ngroups = (N + 320 + 63) / 64;           // padded so windows past the end read zeros
     uint64_t *T3 = arena_alloc<uint64_t>(c, ngroups * 3 + 2);
     uint8_t *Q = arena_alloc<uint8_t>(c, N + 16);
-    uint32_t *SA = d_sa_out ? d_sa_out : arena_alloc<uint32_t>(c, N);
-    uint32_t *ISA = arena_alloc<uint32_t>(c, N + 256);
     uint64_t *keyA = arena_alloc<uint64_t>(c, N), *keyB = arena_alloc<uint64_t>(c, N);
     uint32_t *posA = arena_alloc<uint32_t>(c, N), *posB = arena_alloc<uint32_t>(c, N);
-    uint32_t *slotA = arena_alloc<uint32_t>(c, N), *slotB = arena_alloc<uint32_t>(c, N);
-    uint32_t *gid = arena_alloc<uint32_t>(c, N);
-    const uint32_t rg_tiles_max = div_up(N, RG_TILE);
-    unsigned long long *rg_status = arena_alloc<unsigned long long>(c, (size_t)rg_tiles_max * 3 + 4);
-    uint32_t *rg_counter = (uint32_t *)(rg_status + (size_t)rg_tiles_max * 3);   // [0]=tile ctr [1..2]=totals
+    const uint32_t dcap = (uint32_t)(N / std::min<uint64_t>(GT_E, (uint64_t)c->opt_group_cap + 1) + 64);
+    uint32_t *dtab[2][4];                                   // per level parity: start, len, slot, off
+    for (int a = 0; a < 2; a++)
+        for (int b = 0; b < 4; b++) dtab[a][b] = arena_alloc<uint32_t>(c, dcap + 1);
+    uint32_t *dcount = arena_alloc<uint32_t>(c, 4);
 
     {   // ---- pack: T8/Q, then 3-bit stream (T8 lives in keyB until the first sort needs it)
         uint8_t *T8 = reinterpret_cast<uint8_t *>(keyB);
@@ -399,7 +570,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         BFQ_CUDA(cudaGetLastError());
     }
 
-    // ---- initial sort on k symbols
+    // ---- level 0: global sort on k symbols, groups finished in shared memory
     int k = c->opt_initial_k;
     if (k <= 0) k = 16;
     k = std::min(k, 21);
@@ -410,54 +581,56 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     int flip = radix_sort_pairs64(c, keyA, keyB, posA, posB, N, 3 * k);
     uint64_t *keys = flip ? keyB : keyA, *keys_alt = flip ? keyA : keyB;
     uint32_t *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
-    uint32_t *slot = slotA, *slot_alt = slotB;
 
+    auto words_for = [&](int depth) { return (int)std::max<int64_t>(0, ((int64_t)max_len - depth + 20) / 21); };
+    GroupTileArgs G;
+    memset(&G, 0, sizeof G);
+    G.T3 = T3; G.Q = Q; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
+    G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
+    G.group_cap = (uint32_t)c->opt_group_cap;
+
+    int parity = 0, depth = 0, ksym = k, level = 0;
     uint32_t m = (uint32_t)N;
-    uint32_t h = (uint32_t)k;
-    const int nbits = ceil_log2(N);
-    bool initial = true;
-    int round = 0;
-    while (m > 0) {
-        // regroup the sorted list: ranks, retire singletons, compact the rest
-        const uint32_t tiles = div_up(m, RG_TILE);
-        BFQ_CUDA(cudaMemsetAsync(rg_status, 0, ((size_t)tiles * 3 + 4) * 8, st));
-        uint32_t *ctr = (uint32_t *)(rg_status + (size_t)tiles * 3);
-        {
-            ProfScope ps(c, PC_REGROUP, (uint64_t)m * (8 + 4 + 4 + 4 + 12));
-            if (initial)
-                regroup_kernel<uint64_t, true><<<tiles, RG_THREADS, 0, st>>>(
-                    keys, pos, nullptr, m, ISA, SA, pos_alt, slot_alt, gid, rg_status, ctr, ctr + 1);
-            else
-                regroup_kernel<uint64_t, false><<<tiles, RG_THREADS, 0, st>>>(
-                    keys, pos, slot, m, ISA, SA, pos_alt, slot_alt, gid, rg_status, ctr, ctr + 1);
-        }
-        BFQ_CUDA(cudaGetLastError());
-        BFQ_CUDA(cudaMemcpyAsync(c->h_small, ctr + 1, 8, cudaMemcpyDeviceToHost, st));
+    while (true) {
+        BFQ_CUDA(cudaMemsetAsync(dcount, 0, 16, st));
+        G.pos = pos; G.m = m; G.level0 = level == 0; G.ksym = ksym; G.depth0 = depth;
+        G.W = words_for(depth + ksym);
+        G.g_slot = level ? dtab[parity ^ 1][2] : nullptr;
+        G.g_off = level ? dtab[parity ^ 1][3] : nullptr;
+        G.defer_start = dtab[parity][0];
+        launch_group_tile<uint64_t>(c, keys, G);
+        BFQ_CUDA(cudaMemcpyAsync(c->h_small, dcount, 4, cudaMemcpyDeviceToHost, st));
         BFQ_CUDA(cudaStreamSynchronize(st));
-        const uint32_t kept = ((uint32_t *)c->h_small)[0], groups = ((uint32_t *)c->h_small)[1];
-        std::swap(pos, pos_alt);
-        std::swap(slot, slot_alt);
-        initial = false;
-        m = kept;
-        if (m == 0) break;
-        if (++round > 40) BFQ_FAIL(BFQ_ECUDA, "suffix sort did not converge (internal error)");
-        // next round: sort the survivors by (group, rank of the suffix h further on)
+        const uint32_t ndef = ((uint32_t *)c->h_small)[0];
+        if (ndef == 0) break;
+        if (ndef > dcap) BFQ_FAIL(BFQ_ECUDA, "internal error: %u deferred groups exceed the table of %u", ndef, dcap);
+        if (++level > 64) BFQ_FAIL(BFQ_ECUDA, "suffix sort did not converge (internal error)");
+        // ---- next level: the members of the deferred groups, keyed by (group, next s symbols)
+        uint32_t *dstart = dtab[parity][0], *dlen = dtab[parity][1], *dslot = dtab[parity][2], *doff = dtab[parity][3];
         {
-            ProfScope ps(c, PC_KEYS, (uint64_t)m * (4 + 4 + 4 + 8));
-            doubling_keys_kernel<<<div_up(m, 256), 256, 0, st>>>(pos, gid, ISA, m, h, nbits, keys);
+            ProfScope ps(c, PC_DEFER, 0, 2);
+            defer_len_kernel<uint64_t><<<div_up((uint64_t)ndef * 32, 256), 256, 0, st>>>(
+                keys, m, G.level0, 3 * ksym, G.g_slot, G.g_off, dstart, ndef, dlen, dslot);
+            scan_excl_u32_kernel<<<1, 1024, 0, st>>>(dlen, doff, ndef, dcount + 1);
+            BFQ_CUDA(cudaGetLastError());
         }
-        const int gbits = ceil_log2(groups);
-        flip = radix_sort_pairs64(c, keys, keys_alt, pos, pos_alt, m, nbits + gbits);
-        if (flip) { std::swap(keys, keys_alt); std::swap(pos, pos_alt); }
-        h *= 2;
-    }
-    (void)rg_counter;
-
-    // ---- eBWT, permuted qualities, LCP
-    if (d_bwt) {
-        ProfScope ps(c, PC_GATHER, N * (4 + 3 + 2 + 16));
-        gather_kernel<<<div_up(N, 256), 256, 0, st>>>(SA, T3, Q, (uint32_t)N, eos, c2b, d_bwt, d_qs, d_lcp);
-        BFQ_CUDA(cudaGetLastError());
+        BFQ_CUDA(cudaMemcpyAsync(c->h_small, dcount + 1, 4, cudaMemcpyDeviceToHost, st));
+        BFQ_CUDA(cudaStreamSynchronize(st));
+        const uint32_t m2 = ((uint32_t *)c->h_small)[0];
+        depth += ksym;
+        const int gbits = std::max(1, ceil_log2(ndef));
+        const int s = std::min(21, (64 - gbits) / 3);
+        {
+            ProfScope ps(c, PC_DEFER, (uint64_t)m2 * (4 + 12 + 16));
+            int grid = (int)std::min<uint64_t>(ndef, (uint64_t)c->num_sms * 8);
+            defer_fill_kernel<<<grid, 256, 0, st>>>(pos, dstart, dlen, doff, ndef, T3, depth, s, keys_alt, pos_alt);
+            BFQ_CUDA(cudaGetLastError());
+        }
+        flip = radix_sort_pairs64(c, keys_alt, keys, pos_alt, pos, m2, gbits + 3 * s);
+        if (!flip) { std::swap(keys, keys_alt); std::swap(pos, pos_alt); }
+        m = m2;
+        ksym = s;
+        parity ^= 1;
     }
 }
 

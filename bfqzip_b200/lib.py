@@ -39,7 +39,7 @@ def lib_path(M: int, B: int) -> str:
     return os.path.join(LIBDIR, f"libbfqgpu_M{M}_B{B}.so")
 
 
-PROF_CLASSES = ("radix_pass", "radix_hist", "pack", "keys", "regroup", "gather", "hist", "rank",
+PROF_CLASSES = ("radix_pass", "radix_hist", "pack", "keys", "group", "defer", "hist", "rank",
                 "cluster", "cluster_long", "rule11", "walk", "assemble")
 
 _libs = {}

@@ -79,6 +79,7 @@ int  bfq_ctx_create(bfq_ctx **out, int device);
 void bfq_ctx_destroy(bfq_ctx *ctx);
 /* Tunables (tests use them to force rarely-taken paths).  Unknown key -> BFQ_EINVAL.
  *   "initial_k"   symbols in the initial radix key (1..21, 0 = auto)
+ *   "group_cap"   suffix groups with more members go to the next MSD level even when they fit a tile
  *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
  *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)      */
 int  bfq_ctx_set_option(bfq_ctx *ctx, const char *key, int64_t value);
@@ -123,7 +124,7 @@ int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_qual
 int bfq_export_rows(bfq_ctx *ctx, uint8_t *qs_out, uint8_t *obwt_out);
 
 /* Profile counters, filled when option "profile"=1.  Classes: "radix_pass", "radix_hist",
- * "pack", "keys", "regroup", "gather", "hist", "rank", "cluster", "cluster_long", "rule11",
+ * "pack", "keys", "group", "defer", "hist", "rank", "cluster", "cluster_long", "rule11",
  * "walk", "assemble".  Returns accumulated device ms, launch count and algorithmic bytes
  * since bfq_prof_reset.  Unknown class -> BFQ_EINVAL. */
 int  bfq_prof_get(bfq_ctx *ctx, const char *klass, double *ms, uint64_t *launches, uint64_t *bytes);

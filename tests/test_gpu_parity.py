@@ -72,6 +72,37 @@ def test_part_a_initial_k(k):
     assert np.array_equal(bwt, g["bwt"]) and np.array_equal(qs, g["qs"]) and np.array_equal(lcp, g["lcp"])
 
 
+@pytest.mark.parametrize("cap,k", [(1, 16), (3, 16), (40, 5), (1, 2), (300, 1)])
+@pytest.mark.parametrize("name", ["syn_var_dup", "syn_short"])
+def test_part_a_msd_levels(name, cap, k):
+    """Small group_cap / short keys force the deferred-group (next MSD level) path on every group."""
+    g = np.load(os.path.join(H.GOLDEN, name + ".npz"))
+    c = ctx()
+    c.set_option("group_cap", cap); c.set_option("initial_k", k)
+    try:
+        bwt, qs, lcp = c.build_ebwt(g["bases"], g["quals"], g["off"], 35)
+        sa = c.debug_suffix_array(g["bases"], g["off"])
+    finally:
+        c.set_option("group_cap", 1 << 20); c.set_option("initial_k", 0)
+    assert np.array_equal(bwt, g["bwt"]) and np.array_equal(qs, g["qs"]) and np.array_equal(lcp, g["lcp"])
+    assert np.array_equal(np.sort(sa), np.arange(len(sa), dtype=np.uint32))
+
+
+def test_part_a_huge_groups():
+    """Repeats: groups far larger than a tile (poly-A reads, tandem repeats, many identical reads)."""
+    rng = np.random.default_rng(9)
+    reads = [b"A" * 120] * 900 + [b"ACACACACAC" * 9] * 700 + [b"ACGTTGCA" * 12 + b"N"] * 500
+    reads += [bytes(rng.choice(list(b"ACGT"), size=int(rng.integers(20, 130))).astype(np.uint8)) for _ in range(800)]
+    order = rng.permutation(len(reads))
+    reads = [reads[i] for i in order]
+    bases = np.frombuffer(b"".join(reads), dtype=np.uint8)
+    off = np.zeros(len(reads) + 1, np.uint64); off[1:] = np.cumsum([len(r) for r in reads])
+    quals = rng.integers(35, 74, size=bases.size, dtype=np.uint8)
+    bwt, qs, lcp = ctx().build_ebwt(bases, quals, off, 35)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+
+
 @pytest.mark.parametrize("eos", [0, 35])
 def test_part_a_eos_byte(eos):
     """eGap writes 0, gsufsort '#': identical files otherwise."""
