@@ -236,16 +236,20 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
     uint64_t *s_words = reinterpret_cast<uint64_t *>(gt_smem);                      // [W][GT_S]
-    uint32_t *s_pos = reinterpret_cast<uint32_t *>(s_words + (size_t)A.W * GT_S);   // [GT_S]
-    uint32_t *s_head = s_pos + GT_S;                                                // [GT_HW]
+    uint64_t *s_key = s_words + (size_t)A.W * GT_S;                                 // [GT_S] sort keys of the current order
+    uint32_t *s_pos = reinterpret_cast<uint32_t *>(s_key + GT_S);                   // [GT_S]
+    uint32_t *s_best = s_pos + GT_S;                                                // [GT_S] (length << 16 | member) of a run's reference
+    uint32_t *s_head = s_best + GT_S;                                               // [GT_HW]
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] code | q << 8
     uint16_t *s_gs = s_prev + GT_S;                                                 // [GT_S] group start or 0xFFFF
     uint16_t *s_sorted = s_gs + GT_S;                                               // [GT_S] member at sorted row
-    uint16_t *s_idx = s_sorted + GT_S;                                              // [2*GT_S] bitonic scratch
-    uint16_t *s_gstart = s_idx + 2 * GT_S;                                          // [GT_GMAX]
+    uint16_t *s_runa = s_sorted + GT_S;                                             // [GT_S] first row of the run a row is in
+    uint16_t *s_gstart = s_runa + GT_S;                                             // [GT_GMAX]
     uint16_t *s_glen = s_gstart + GT_GMAX;                                          // [GT_GMAX]
-    uint16_t *s_gscr = s_glen + GT_GMAX;                                            // [GT_GMAX]
-    __shared__ uint32_t s_ngroups, s_scrtop, s_next;
+    uint8_t *s_len = reinterpret_cast<uint8_t *>(s_glen + GT_GMAX);                 // [GT_S] staged symbols before the terminator
+    uint8_t *s_rdepth = s_len + GT_S;                                               // [GT_S] depth of the row's run, 0xFF = resolved
+    uint8_t *s_lcpout = s_rdepth + GT_S;                                            // [GT_S] LCP with the previous sorted row (staged part)
+    __shared__ uint32_t s_ngroups, s_next;
 
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t t0 = blockIdx.x * (uint32_t)GT_T;
@@ -253,7 +257,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     const int W = A.W, ksym = A.ksym;
     const int depth = A.depth0 + ksym;
     const int kshift = 3 * ksym;                          // group id sits above the symbols (level >= 1)
-    if (tid == 0) { s_ngroups = 0; s_scrtop = 0; s_next = 0; }
+    if (tid == 0) { s_ngroups = 0; s_next = 0; }
 
     // ---- phase 0: head bitmap of the staged window (bit r <=> list slot t0 + r starts a group)
     for (int base = 0; base < GT_HW * 32; base += GT_THREADS) {
@@ -312,11 +316,8 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                     }
                     if (size > 1) {
                         if (fits) {
-                            uint32_t n2 = 2;
-                            while ((int)n2 < size) n2 <<= 1;
                             const uint32_t g = atomicAdd(&s_ngroups, 1u);
                             s_gstart[g] = (uint16_t)gs; s_glen[g] = (uint16_t)size;
-                            s_gscr[g] = (uint16_t)atomicAdd(&s_scrtop, n2);
                         } else {
                             const uint32_t d = atomicAdd(A.defer_count, 1u);
                             if (d < A.defer_cap) A.defer_start[d] = (uint32_t)j;
@@ -336,10 +337,14 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                     s_prev[r] = (uint16_t)(c | ((uint32_t)q << 8));
                     if (size > 1) {
                         bool term = false;
+                        int slen = 0;
                         for (int w = 0; w < W; w++) {
                             uint64_t x = term ? 0ull : text_window(A.T3, (uint64_t)p + depth + 21 * w);
-                            s_words[w * GT_S + r] = cut_at_terminator(x, term);
+                            x = cut_at_terminator(x, term);
+                            s_words[w * GT_S + r] = x;
+                            slen += leading_nonzero_fields(x);
                         }
+                        s_len[r] = (uint8_t)slen;
                     }
                 }
             }
@@ -348,42 +353,131 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     }
     __syncthreads();
 
-    // ---- phase 2: one warp sorts one group (bitonic over member indices, +inf padding)
+    // ---- phase 2: one warp orders one group.
+    // Rows of a group start in position order as ONE unresolved run at depth 0.  Per iteration every
+    // member of an unresolved run is compared once with the run's REFERENCE (its longest member):
+    // l = common prefix, c / r = the member's / the reference's symbol at l (0 = terminator).  With
+    //   type L (c < r): before the reference, ordered by (l ascending, c)
+    //   type E (c = r = 0): identical to the reference
+    //   type G (c > r): after it, ordered by (l descending, c)
+    // the key (run, type, l', c, position index) sorts the run; members with equal (type, l, c != 0)
+    // share l + 1 symbols and form a new run for the next iteration, everything else is final.  Two
+    // neighbours that end up with different key classes have LCP = min(l, l') -- no string compare.
+    // Typical read data: the members are prefixes of the longest one -> one iteration.
     const uint32_t ngroups = s_ngroups;
-    auto less = [&](uint32_t a, uint32_t b) -> bool {
-        if (a == 0xFFFFu) return false;
-        if (b == 0xFFFFu) return true;
-        for (int w = 0; w < W; w++) {
-            const uint64_t wa = s_words[w * GT_S + a], wb = s_words[w * GT_S + b];
-            if (wa != wb) return wa < wb;
-        }
-        return s_pos[a] < s_pos[b];
-    };
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&s_next, 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
         const uint32_t gs = s_gstart[g], len = s_glen[g];
-        uint16_t *idx = s_idx + s_gscr[g];
         uint32_t n2 = 2;
         while (n2 < len) n2 <<= 1;
-        for (uint32_t i = lane; i < n2; i += 32) idx[i] = i < len ? (uint16_t)(gs + i) : (uint16_t)0xFFFF;
+        for (uint32_t t = lane; t < len; t += 32) { s_runa[gs + t] = (uint16_t)gs; s_rdepth[gs + t] = 0; s_key[gs + t] = t; }
+        if (lane == 0) s_best[gs] = 0;
         __syncwarp();
-        for (uint32_t k = 2; k <= n2; k <<= 1) {
-            for (uint32_t jj = k >> 1; jj > 0; jj >>= 1) {
+        while (true) {
+            // A: reference of every unresolved run
+            for (uint32_t t = lane; t < len; t += 32) {
+                const uint32_t row = gs + t;
+                if (s_rdepth[row] != 0xFF) {
+                    const uint32_t mem = gs + (uint32_t)(s_key[row] & 0x7FFu);
+                    atomicMax(&s_best[s_runa[row]], ((uint32_t)s_len[mem] << 16) | mem);
+                }
+            }
+            __syncwarp();
+            // B: keys
+            for (uint32_t t = lane; t < len; t += 32) {
+                const uint32_t row = gs + t;
+                const uint32_t idx = (uint32_t)(s_key[row] & 0x7FFu);
+                const uint32_t D = s_rdepth[row];
+                uint64_t nk;
+                if (D == 0xFF) nk = ((uint64_t)t << 24) | idx;
+                else {
+                    const uint32_t mem = gs + idx, a = s_runa[row], ref = s_best[a] & 0xFFFFu;
+                    uint32_t l = 21u * (uint32_t)W, c = 0, rr = 0;
+                    for (int j = (int)(D / 21u); j < W; j++) {
+                        const uint64_t wa = s_words[j * GT_S + mem], wb = s_words[j * GT_S + ref];
+                        const uint64_t x = wa ^ wb;
+                        const int fm = x ? (__clzll((long long)x) / 3) : 21;
+                        const int step = min(fm, min(leading_nonzero_fields(wa), leading_nonzero_fields(wb)));
+                        if (step < 21) {
+                            l = 21u * j + step;
+                            const int sh = 61 - 3 * step;
+                            c = (uint32_t)(wa >> sh) & 7u; rr = (uint32_t)(wb >> sh) & 7u;
+                            break;
+                        }
+                    }
+                    const uint32_t type = c < rr ? 0u : (c == rr ? 1u : 2u);
+                    const uint32_t lkey = type == 2u ? 255u - l : l;
+                    nk = ((uint64_t)(a - gs) << 24) | ((uint64_t)type << 22) | ((uint64_t)lkey << 14) | ((uint64_t)c << 11) | idx;
+                }
+                s_key[row] = nk;
+            }
+            __syncwarp();
+            // C: bitonic network with ascending comparators only (rows >= len act as +inf and never move)
+            uint64_t *key = s_key + gs;
+            for (uint32_t k = 2; k <= n2; k <<= 1) {
+                const uint32_t half = k >> 1;
                 for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
-                    const uint32_t i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
-                    const uint32_t l = i | jj;
-                    const uint32_t a = idx[i], b = idx[l];
-                    const bool up = (i & k) == 0;
-                    const bool sw = up ? less(b, a) : less(a, b);
-                    if (sw) { idx[i] = (uint16_t)b; idx[l] = (uint16_t)a; }
+                    const uint32_t i = ((t & ~(half - 1)) << 1) | (t & (half - 1));
+                    const uint32_t l = i ^ (k - 1);
+                    if (l < len) { const uint64_t x = key[i], y = key[l]; if (y < x) { key[i] = y; key[l] = x; } }
                 }
                 __syncwarp();
+                for (uint32_t jj = half >> 1; jj > 0; jj >>= 1) {
+                    for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
+                        const uint32_t i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
+                        const uint32_t l = i | jj;
+                        if (l < len) { const uint64_t x = key[i], y = key[l]; if (y < x) { key[i] = y; key[l] = x; } }
+                    }
+                    __syncwarp();
+                }
             }
+            // D: new runs, final LCPs
+            bool any = false;
+            uint32_t carry = gs;
+            for (uint32_t base = 0; base < len; base += 32) {
+                const uint32_t t = base + lane, row = gs + t;
+                const bool valid = t < len;
+                bool start = true, unres = false;
+                uint32_t newdepth = 0xFF;
+                if (valid && s_rdepth[row] != 0xFF) {
+                    const uint32_t olda = s_runa[row];
+                    const uint32_t kt = (uint32_t)(s_key[row] >> 11);
+                    const uint32_t c = kt & 7u, ty = (kt >> 11) & 3u, lk = (kt >> 3) & 255u;
+                    const uint32_t l = ty == 2u ? 255u - lk : lk;
+                    bool tiedprev = false;
+                    if (row > olda) {
+                        const uint32_t kp = (uint32_t)(s_key[row - 1] >> 11);
+                        tiedprev = kp == kt && c != 0;
+                        if (!tiedprev) {
+                            const uint32_t tp = (kp >> 11) & 3u, lp = (kp >> 3) & 255u;
+                            s_lcpout[row] = (uint8_t)min(l, tp == 2u ? 255u - lp : lp);
+                        }
+                    }
+                    const bool tiednext = t + 1 < len && s_runa[row + 1] == olda && s_rdepth[row + 1] != 0xFF &&
+                                          (uint32_t)(s_key[row + 1] >> 11) == kt && c != 0;
+                    start = !tiedprev;
+                    unres = tiedprev || tiednext;
+                    newdepth = l + 1;
+                }
+                const uint32_t bits = __ballot_sync(0xffffffffu, valid && start);
+                const uint32_t below = bits & (0xffffffffu >> (31 - lane));
+                const uint32_t anew = below ? gs + base + 31 - __clz(below) : carry;
+                __syncwarp();
+                if (valid) {
+                    s_runa[row] = (uint16_t)anew;
+                    s_rdepth[row] = unres ? (uint8_t)newdepth : (uint8_t)0xFF;
+                    if (start && unres) s_best[row] = 0;
+                }
+                if (bits) carry = gs + base + 31 - __clz(bits);
+                any |= unres;
+            }
+            __syncwarp();
+            if (!__any_sync(0xffffffffu, any)) break;
         }
-        for (uint32_t i = lane; i < len; i += 32) s_sorted[gs + i] = idx[i];
+        for (uint32_t t = lane; t < len; t += 32) s_sorted[gs + t] = (uint16_t)(gs + (uint32_t)(s_key[gs + t] & 0x7FFu));
         __syncwarp();
     }
     __syncthreads();
@@ -401,15 +495,15 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
             const uint32_t c = pv & 7u;
             A.bwt[slot] = c ? (uint8_t)(A.code2byte >> (8 * c)) : A.eos;
             A.qs[slot] = (uint8_t)(pv >> 8);
-            if ((uint32_t)r != gs) A.lcp[slot] = (uint8_t)(depth + staged_lcp(s_words, W, s_sorted[r - 1], e));
+            if ((uint32_t)r != gs) A.lcp[slot] = (uint8_t)(depth + s_lcpout[r]);
         }
     }
 }
 
 static size_t group_tile_smem(int W)
 {
-    return (size_t)W * GT_S * 8 + (size_t)GT_S * 4 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 3 +
-           (size_t)2 * GT_S * 2 + (size_t)GT_GMAX * 2 * 3;
+    return (size_t)W * GT_S * 8 + (size_t)GT_S * 8 + (size_t)GT_S * 4 * 2 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 +
+           (size_t)GT_GMAX * 2 * 2 + (size_t)GT_S * 3 + 16;
 }
 
 // ============================================================================ deferred groups
@@ -535,6 +629,9 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     const uint64_t N = total_bases + nreads;
     if (N == 0) return;
     if (N >= ((uint64_t)1 << 32) - 64) BFQ_FAIL(BFQ_ETOOLARGE, "collection has %llu rows; this build indexes rows with 32 bits", (unsigned long long)N);
+    if (max_len > 255)
+        BFQ_FAIL(BFQ_EINVAL, "a read has %llu symbols; reads are limited to 255 (1-byte LCP entries, dataTypelenSeq is uchar, parameters.h:68)",
+                 (unsigned long long)max_len);
     cudaStream_t st = c->stream;
 
     // ---- alphabet from the data (codes follow byte order, like gsufsort's +1 remap)
