@@ -16,7 +16,7 @@
 //
 // Layouts in HBM (N = sum(len+1) rows, N < 2^32):
 //   T3   3-bit codes, big-endian bit stream, 64 symbols per three u64 words (fits L2 for cfg2)
-//   Q    N bytes, quality of position p (EOS byte at terminators)
+//   QL   u16[N], quality of position p-1 | (symbols from p to its terminator) << 8
 //   key  u64[N] x2, pos u32[N] x2   sort ping-pong: (k-symbol key, text position)
 //   level >= 1 lists (members of groups too large for one tile) reuse the same ping-pong pair
 #include "common.cuh"
@@ -65,11 +65,12 @@ void byte_histogram(bfq_ctx *c, const uint8_t *d_data, uint64_t n, uint64_t hist
 // ============================================================================ text packing
 struct Lut256 { uint8_t v[256]; };
 
-// one warp per read: T8[p] = code, Q[p] = quality; terminator code 0 / EOS byte after the read
+// one warp per read: T8[p] = code (terminator code 0 after the read);
+// QL[p] = quality of position p-1 | (symbols from p to the read's terminator) << 8
 __global__ void __launch_bounds__(256)
 pack_reads_kernel(const uint8_t *__restrict__ bases, const uint8_t *__restrict__ quals,
                   const uint64_t *__restrict__ off, uint64_t nreads, Lut256 lut, uint8_t eos,
-                  uint8_t *__restrict__ T8, uint8_t *__restrict__ Q)
+                  uint8_t *__restrict__ T8, uint16_t *__restrict__ QL)
 {
     __shared__ uint8_t s_lut[256];
     s_lut[threadIdx.x] = lut.v[threadIdx.x];
@@ -81,9 +82,9 @@ pack_reads_kernel(const uint8_t *__restrict__ bases, const uint8_t *__restrict__
         const uint64_t s = off[d], e = off[d + 1], len = e - s, dst = s + d;
         for (uint64_t j = lane; j < len; j += 32) {
             T8[dst + j] = s_lut[bases[s + j]];
-            Q[dst + j] = quals[s + j];
+            QL[dst + j] = (uint16_t)((j ? quals[s + j - 1] : eos) | ((len - j) << 8));
         }
-        if (lane == 0) { T8[dst + len] = 0; Q[dst + len] = eos; }
+        if (lane == 0) { T8[dst + len] = 0; QL[dst + len] = quals[e - 1]; }
     }
 }
 
@@ -168,7 +169,7 @@ init_keys_kernel(const uint64_t *__restrict__ T3, uint32_t n, int k, K *__restri
 // symbols as key (MSD recursion; at most ceil(max_len / 14) levels, only repeats get there).
 constexpr int GT_THREADS = 256;
 constexpr int GT_T = 1024;
-constexpr int GT_E = 512;
+constexpr int GT_E = 256;
 constexpr int GT_S = GT_T + GT_E;
 constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
 constexpr int GT_GMAX = GT_S / 2;
@@ -181,7 +182,7 @@ struct GroupTileArgs {
     int depth0;                 // symbols known equal before this key (0 at level 0)
     int W;                      // words of 21 symbols to stage per member
     const uint64_t *T3;
-    const uint8_t *Q;
+    const uint16_t *QL;         // per text position p: quality of p-1 | (symbols from p to its terminator) << 8
     const uint32_t *g_slot;     // level >= 1: SA slot of the first member of list group g
     const uint32_t *g_off;      // level >= 1: list offset of the first member of list group g
     uint32_t *SA;               // optional
@@ -202,21 +203,6 @@ __device__ __forceinline__ uint64_t cut_at_terminator(uint64_t w, bool &terminat
     return w;
 }
 
-// common prefix (in symbols, terminators not counted) of two staged strings
-__device__ __forceinline__ uint32_t staged_lcp(const uint64_t *s_words, int W, uint32_t a, uint32_t b)
-{
-    uint32_t l = 0;
-    for (int j = 0; j < W; j++) {
-        const uint64_t wa = s_words[j * GT_S + a], wb = s_words[j * GT_S + b];
-        const uint64_t x = wa ^ wb;
-        const int fm = x ? (__clzll((long long)x) / 3) : 21;
-        const int step = min(fm, min(leading_nonzero_fields(wa), leading_nonzero_fields(wb)));
-        l += step;
-        if (step < 21) break;
-    }
-    return l;
-}
-
 // LCP of the head of a group with the row before it, from the two keys (symbol parts)
 template <typename K>
 __device__ __forceinline__ uint32_t head_lcp(K kprev, K kcur, int ksym)
@@ -230,18 +216,268 @@ __device__ __forceinline__ uint32_t head_lcp(K kprev, K kcur, int ksym)
     return (uint32_t)min(min(fm, z), ksym);
 }
 
+// ---- in-group ordering -------------------------------------------------------------------
+// Rows of a group start in position order as ONE unresolved run at depth 0.  Per iteration every
+// member of an unresolved run is compared once with the run's REFERENCE (its longest member):
+// l = common prefix, c / r = the member's / the reference's symbol at l (0 = terminator).  With
+//   type L (c < r): before the reference, ordered by (l ascending, c)
+//   type E (c = r = 0): identical to the reference
+//   type G (c > r): after it, ordered by (l descending, c)
+// the key (run, type, l', c, position index) sorts the run; members with equal (run, type, l, c != 0)
+// share l + 1 symbols and form a new run for the next iteration, everything else is final.  Two
+// neighbours with different key classes have LCP = min(l, l') -- no string compare.  Typical read
+// data: most members are prefixes of the longest one and a single iteration resolves the group.
+struct RefCmp { uint32_t l, c, r; };
+
+__device__ __forceinline__ RefCmp ref_compare(const uint64_t *s_words, const uint8_t *s_len, int W,
+                                              uint32_t mem, uint32_t ref, uint32_t D)
+{
+    const uint32_t lm = s_len[mem], lr = s_len[ref];
+    const uint32_t lmin = min(lm, lr);
+    RefCmp o;
+    o.l = lmin;
+    const int jend = min(W, (int)(lmin / 21u) + 1);      // a difference cannot lie past the shorter string's terminator
+    for (int j = (int)(D / 21u); j < jend; j++) {
+        const uint64_t x = s_words[j * GT_S + mem] ^ s_words[j * GT_S + ref];
+        if (x) { o.l = min(lmin, 21u * j + (uint32_t)(__clzll((long long)x) / 3)); break; }
+    }
+    const uint32_t j = o.l / 21u;
+    const int sh = 61 - 3 * (int)(o.l - 21u * j);
+    o.c = o.l < lm ? (uint32_t)(s_words[j * GT_S + mem] >> sh) & 7u : 0u;
+    o.r = o.l < lr ? (uint32_t)(s_words[j * GT_S + ref] >> sh) & 7u : 0u;
+    return o;
+}
+
+// Key fields above the position index (IB bits): c [2:0], l' [10:3], type [12:11], run [..:13]
+__device__ __forceinline__ uint32_t class_of(const RefCmp &o)
+{
+    const uint32_t type = o.c < o.r ? 0u : (o.c == o.r ? 1u : 2u);
+    const uint32_t lkey = type == 2u ? 255u - o.l : o.l;
+    return (type << 11) | (lkey << 3) | o.c;
+}
+__device__ __forceinline__ uint32_t class_l(uint32_t cls)
+{
+    const uint32_t lk = (cls >> 3) & 255u;
+    return ((cls >> 11) & 3u) == 2u ? 255u - lk : lk;
+}
+
+// groups of at most 32 * R rows: one row per (slot, lane), keys in registers, shuffles only
+template <int R>
+__device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int W, const uint64_t *s_words,
+                                                 const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
+                                                 uint8_t *s_lcpout)
+{
+    constexpr uint32_t IB = 6, IM = 63u;                  // position index bits
+    uint32_t key[R], runa[R], rdepth[R];
+#pragma unroll
+    for (int s = 0; s < R; s++) {
+        const uint32_t t = s * 32 + lane;
+        key[s] = t < len ? t : 0xFFFFFFFFu;
+        runa[s] = 0;
+        rdepth[s] = t < len ? 0u : 0xFFu;
+    }
+    if (lane == 0) s_best[gs] = 0;
+    __syncwarp();
+    while (true) {
+#pragma unroll
+        for (int s = 0; s < R; s++)
+            if (rdepth[s] != 0xFFu) {
+                const uint32_t mem = gs + (key[s] & IM);
+                atomicMax(&s_best[gs + runa[s]], ((uint32_t)s_len[mem] << 16) | mem);
+            }
+        __syncwarp();
+#pragma unroll
+        for (int s = 0; s < R; s++) {
+            const uint32_t t = s * 32 + lane;
+            if (t < len) {
+                const uint32_t idx = key[s] & IM;
+                if (rdepth[s] == 0xFFu) key[s] = (t << (13 + IB)) | idx;
+                else {
+                    const RefCmp o = ref_compare(s_words, s_len, W, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
+                    key[s] = (runa[s] << (13 + IB)) | (class_of(o) << IB) | idx;
+                }
+            }
+        }
+        // bitonic network, ascending comparators only (rows >= len hold +inf and never move)
+#pragma unroll
+        for (uint32_t k = 2; k <= 32u * R; k <<= 1) {
+            if ((k >> 1) >= len) break;
+            const uint32_t half = k >> 1;
+            if (k <= 32) {
+#pragma unroll
+                for (int s = 0; s < R; s++) {
+                    const uint32_t o = __shfl_xor_sync(0xffffffffu, key[s], k - 1);
+                    key[s] = (lane & half) ? max(key[s], o) : min(key[s], o);
+                }
+            } else {                                      // k == 64: partner = other slot, lane ^ 31
+                const uint32_t o0 = __shfl_xor_sync(0xffffffffu, key[R - 1], 31);
+                const uint32_t o1 = __shfl_xor_sync(0xffffffffu, key[0], 31);
+                key[0] = min(key[0], o0);
+                key[R - 1] = max(key[R - 1], o1);
+            }
+#pragma unroll
+            for (uint32_t jj = 16; jj > 0; jj >>= 1) {
+                if (jj < half) {
+#pragma unroll
+                    for (int s = 0; s < R; s++) {
+                        const uint32_t o = __shfl_xor_sync(0xffffffffu, key[s], jj);
+                        key[s] = (lane & jj) ? max(key[s], o) : min(key[s], o);
+                    }
+                }
+            }
+        }
+        // new runs and final LCPs
+        bool any = false;
+        uint32_t startbits[R];
+        uint32_t cls[R];
+        bool st[R], un[R];
+#pragma unroll
+        for (int s = 0; s < R; s++) {
+            const uint32_t t = s * 32 + lane;
+            uint32_t prevk = __shfl_up_sync(0xffffffffu, key[s], 1);
+            uint32_t nextk = __shfl_down_sync(0xffffffffu, key[s], 1);
+            if (s > 0) { const uint32_t x = __shfl_sync(0xffffffffu, key[s - 1], 31); if (lane == 0) prevk = x; }
+            if (s + 1 < R) { const uint32_t x = __shfl_sync(0xffffffffu, key[s + 1], 0); if (lane == 31) nextk = x; }
+            else if (lane == 31) nextk = 0xFFFFFFFFu;
+            st[s] = true; un[s] = false; cls[s] = 0;
+            if (t < len && rdepth[s] != 0xFFu) {
+                const uint32_t kt = key[s] >> IB;
+                cls[s] = kt & 0x1FFFu;
+                const bool open = (kt & 7u) != 0;
+                bool tiedprev = false;
+                if (t > runa[s]) {
+                    const uint32_t kp = prevk >> IB;
+                    tiedprev = kp == kt && open;
+                    if (!tiedprev) s_lcpout[gs + t] = (uint8_t)min(class_l(kt), class_l(kp));
+                }
+                const bool tiednext = (nextk >> IB) == kt && open;
+                st[s] = !tiedprev;
+                un[s] = tiedprev || tiednext;
+            }
+            startbits[s] = __ballot_sync(0xffffffffu, t < len && st[s]);
+            any |= un[s];
+        }
+#pragma unroll
+        for (int s = 0; s < R; s++) {
+            const uint32_t t = s * 32 + lane;
+            if (t < len) {
+                const uint32_t below = startbits[s] & (0xffffffffu >> (31 - lane));
+                uint32_t a = below ? s * 32 + 31 - __clz(below) : 0u;
+                if (!below && s > 0) a = 31 - __clz(startbits[0]);          // R <= 2: the run began in slot 0
+                runa[s] = a;
+                rdepth[s] = un[s] ? class_l(cls[s]) + 1 : 0xFFu;
+                if (st[s] && un[s]) s_best[gs + t] = 0;
+            }
+        }
+        __syncwarp();
+        if (!__any_sync(0xffffffffu, any)) break;
+    }
+#pragma unroll
+    for (int s = 0; s < R; s++) {
+        const uint32_t t = s * 32 + lane;
+        if (t < len) s_sorted[gs + t] = (uint16_t)(gs + (key[s] & IM));
+    }
+}
+
+// groups of any size that fits the window: keys in shared memory, lanes stride over the rows
+__device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int lane, int W, const uint64_t *s_words,
+                                                 const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
+                                                 uint8_t *s_lcpout, uint64_t *s_key, uint16_t *s_runa, uint8_t *s_rdepth)
+{
+    uint32_t n2 = 2;
+    while (n2 < len) n2 <<= 1;
+    for (uint32_t t = lane; t < len; t += 32) { s_runa[gs + t] = (uint16_t)gs; s_rdepth[gs + t] = 0; s_key[gs + t] = t; }
+    if (lane == 0) s_best[gs] = 0;
+    __syncwarp();
+    uint64_t *key = s_key + gs;
+    while (true) {
+        for (uint32_t t = lane; t < len; t += 32) {
+            const uint32_t row = gs + t;
+            if (s_rdepth[row] != 0xFF) {
+                const uint32_t mem = gs + (uint32_t)(key[t] & 0x7FFu);
+                atomicMax(&s_best[s_runa[row]], ((uint32_t)s_len[mem] << 16) | mem);
+            }
+        }
+        __syncwarp();
+        for (uint32_t t = lane; t < len; t += 32) {
+            const uint32_t row = gs + t;
+            const uint32_t idx = (uint32_t)(key[t] & 0x7FFu);
+            const uint32_t D = s_rdepth[row];
+            if (D == 0xFF) key[t] = ((uint64_t)t << 24) | idx;
+            else {
+                const uint32_t a = s_runa[row];
+                const RefCmp o = ref_compare(s_words, s_len, W, gs + idx, s_best[a] & 0xFFFFu, D);
+                key[t] = ((uint64_t)(a - gs) << 24) | ((uint64_t)class_of(o) << 11) | idx;
+            }
+        }
+        __syncwarp();
+        for (uint32_t k = 2; k <= n2; k <<= 1) {
+            const uint32_t half = k >> 1;
+            for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
+                const uint32_t i = ((t & ~(half - 1)) << 1) | (t & (half - 1));
+                const uint32_t l = i ^ (k - 1);
+                if (l < len) { const uint64_t x = key[i], y = key[l]; if (y < x) { key[i] = y; key[l] = x; } }
+            }
+            __syncwarp();
+            for (uint32_t jj = half >> 1; jj > 0; jj >>= 1) {
+                for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
+                    const uint32_t i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
+                    const uint32_t l = i | jj;
+                    if (l < len) { const uint64_t x = key[i], y = key[l]; if (y < x) { key[i] = y; key[l] = x; } }
+                }
+                __syncwarp();
+            }
+        }
+        bool any = false;
+        uint32_t carry = gs;
+        for (uint32_t base = 0; base < len; base += 32) {
+            const uint32_t t = base + lane, row = gs + t;
+            const bool valid = t < len;
+            bool start = true, unres = false;
+            uint32_t newdepth = 0xFF;
+            if (valid && s_rdepth[row] != 0xFF) {
+                const uint32_t kt = (uint32_t)(key[t] >> 11);
+                const bool open = (kt & 7u) != 0;
+                bool tiedprev = false;
+                if (row > s_runa[row]) {
+                    const uint32_t kp = (uint32_t)(key[t - 1] >> 11);
+                    tiedprev = kp == kt && open;
+                    if (!tiedprev) s_lcpout[row] = (uint8_t)min(class_l(kt), class_l(kp));
+                }
+                const bool tiednext = t + 1 < len && (uint32_t)(key[t + 1] >> 11) == kt && open;
+                start = !tiedprev;
+                unres = tiedprev || tiednext;
+                newdepth = class_l(kt) + 1;
+            }
+            const uint32_t bits = __ballot_sync(0xffffffffu, valid && start);
+            const uint32_t below = bits & (0xffffffffu >> (31 - lane));
+            const uint32_t anew = below ? gs + base + 31 - __clz(below) : carry;
+            __syncwarp();
+            if (valid) {
+                s_runa[row] = (uint16_t)anew;
+                s_rdepth[row] = unres ? (uint8_t)newdepth : (uint8_t)0xFF;
+                if (start && unres) s_best[row] = 0;
+            }
+            if (bits) carry = gs + base + 31 - __clz(bits);
+            any |= unres;
+        }
+        __syncwarp();
+        if (!__any_sync(0xffffffffu, any)) break;
+    }
+    for (uint32_t t = lane; t < len; t += 32) s_sorted[gs + t] = (uint16_t)(gs + (uint32_t)(key[t] & 0x7FFu));
+}
+
 template <typename K>
 __global__ void __launch_bounds__(GT_THREADS)
 group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
-    uint64_t *s_words = reinterpret_cast<uint64_t *>(gt_smem);                      // [W][GT_S]
-    uint64_t *s_key = s_words + (size_t)A.W * GT_S;                                 // [GT_S] sort keys of the current order
-    uint32_t *s_pos = reinterpret_cast<uint32_t *>(s_key + GT_S);                   // [GT_S]
-    uint32_t *s_best = s_pos + GT_S;                                                // [GT_S] (length << 16 | member) of a run's reference
+    uint64_t *s_words = reinterpret_cast<uint64_t *>(gt_smem);                      // [W][GT_S] staged suffix words
+    uint64_t *s_key = s_words + (size_t)A.W * GT_S;                                 // [GT_S] keys of groups > 64 rows
+    uint32_t *s_best = reinterpret_cast<uint32_t *>(s_key + GT_S);                  // [GT_S] (length << 16 | row) of a run's reference
     uint32_t *s_head = s_best + GT_S;                                               // [GT_HW]
-    uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] code | q << 8
-    uint16_t *s_gs = s_prev + GT_S;                                                 // [GT_S] group start or 0xFFFF
+    uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] previous symbol code | its quality << 8
+    uint16_t *s_gs = s_prev + GT_S;                                                 // [GT_S] group start or 0xFFFF (row not owned)
     uint16_t *s_sorted = s_gs + GT_S;                                               // [GT_S] member at sorted row
     uint16_t *s_runa = s_sorted + GT_S;                                             // [GT_S] first row of the run a row is in
     uint16_t *s_gstart = s_runa + GT_S;                                             // [GT_GMAX]
@@ -273,7 +509,6 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     }
     __syncthreads();
 
-    auto is_head = [&](int r) -> bool { return (s_head[r >> 5] >> (r & 31)) & 1u; };
     auto next_head = [&](int r) -> int {                  // first head > r (exists: sentinel region)
         int w = (r + 1) >> 5;
         uint32_t bits = s_head[w] & (0xffffffffu << ((r + 1) & 31));
@@ -292,7 +527,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         return A.g_slot[g] + (j - A.g_off[g]);
     };
 
-    // ---- phase 1: ownership, group list, staging of positions / previous symbol / suffix words
+    // ---- phase 1: ownership, group list, staging of previous symbol / suffix words
     for (int r = tid; r < GT_S; r += GT_THREADS) {
         const uint64_t j = (uint64_t)t0 + r;
         uint16_t gs16 = 0xFFFF;
@@ -327,24 +562,24 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                 if (fits) {
                     gs16 = (uint16_t)gs;
                     const uint32_t p = A.pos[j];
-                    s_pos[r] = p;
                     s_sorted[r] = (uint16_t)r;
-                    uint32_t c = 0; uint8_t q = A.eos;
-                    if (A.bwt && p > 0) {
-                        c = sym_code(A.T3, (uint64_t)p - 1);
-                        if (c) q = A.Q[p - 1];
+                    const uint32_t ql = A.QL[p];
+                    if (A.bwt) {
+                        const uint32_t c = p > 0 ? sym_code(A.T3, (uint64_t)p - 1) : 0u;
+                        s_prev[r] = (uint16_t)(c | ((c ? (ql & 255u) : (uint32_t)A.eos) << 8));
                     }
-                    s_prev[r] = (uint16_t)(c | ((uint32_t)q << 8));
                     if (size > 1) {
-                        bool term = false;
-                        int slen = 0;
-                        for (int w = 0; w < W; w++) {
-                            uint64_t x = term ? 0ull : text_window(A.T3, (uint64_t)p + depth + 21 * w);
-                            x = cut_at_terminator(x, term);
-                            s_words[w * GT_S + r] = x;
-                            slen += leading_nonzero_fields(x);
-                        }
+                        const int slen = (int)(ql >> 8) - depth;          // symbols of this suffix past the shared prefix
                         s_len[r] = (uint8_t)slen;
+                        for (int w = 0; w < W; w++) {
+                            const int v = slen - 21 * w;                     // valid symbols in this word
+                            uint64_t x = 0;
+                            if (v > 0) {
+                                x = text_window(A.T3, (uint64_t)p + depth + 21 * w);
+                                if (v < 21) x &= ~0ull << (64 - 3 * v);
+                            }
+                            s_words[w * GT_S + r] = x;
+                        }
                     }
                 }
             }
@@ -353,17 +588,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     }
     __syncthreads();
 
-    // ---- phase 2: one warp orders one group.
-    // Rows of a group start in position order as ONE unresolved run at depth 0.  Per iteration every
-    // member of an unresolved run is compared once with the run's REFERENCE (its longest member):
-    // l = common prefix, c / r = the member's / the reference's symbol at l (0 = terminator).  With
-    //   type L (c < r): before the reference, ordered by (l ascending, c)
-    //   type E (c = r = 0): identical to the reference
-    //   type G (c > r): after it, ordered by (l descending, c)
-    // the key (run, type, l', c, position index) sorts the run; members with equal (type, l, c != 0)
-    // share l + 1 symbols and form a new run for the next iteration, everything else is final.  Two
-    // neighbours that end up with different key classes have LCP = min(l, l') -- no string compare.
-    // Typical read data: the members are prefixes of the longest one -> one iteration.
+    // ---- phase 2: one warp orders one group
     const uint32_t ngroups = s_ngroups;
     while (true) {
         uint32_t g = 0;
@@ -371,113 +596,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
         const uint32_t gs = s_gstart[g], len = s_glen[g];
-        uint32_t n2 = 2;
-        while (n2 < len) n2 <<= 1;
-        for (uint32_t t = lane; t < len; t += 32) { s_runa[gs + t] = (uint16_t)gs; s_rdepth[gs + t] = 0; s_key[gs + t] = t; }
-        if (lane == 0) s_best[gs] = 0;
-        __syncwarp();
-        while (true) {
-            // A: reference of every unresolved run
-            for (uint32_t t = lane; t < len; t += 32) {
-                const uint32_t row = gs + t;
-                if (s_rdepth[row] != 0xFF) {
-                    const uint32_t mem = gs + (uint32_t)(s_key[row] & 0x7FFu);
-                    atomicMax(&s_best[s_runa[row]], ((uint32_t)s_len[mem] << 16) | mem);
-                }
-            }
-            __syncwarp();
-            // B: keys
-            for (uint32_t t = lane; t < len; t += 32) {
-                const uint32_t row = gs + t;
-                const uint32_t idx = (uint32_t)(s_key[row] & 0x7FFu);
-                const uint32_t D = s_rdepth[row];
-                uint64_t nk;
-                if (D == 0xFF) nk = ((uint64_t)t << 24) | idx;
-                else {
-                    const uint32_t mem = gs + idx, a = s_runa[row], ref = s_best[a] & 0xFFFFu;
-                    uint32_t l = 21u * (uint32_t)W, c = 0, rr = 0;
-                    for (int j = (int)(D / 21u); j < W; j++) {
-                        const uint64_t wa = s_words[j * GT_S + mem], wb = s_words[j * GT_S + ref];
-                        const uint64_t x = wa ^ wb;
-                        const int fm = x ? (__clzll((long long)x) / 3) : 21;
-                        const int step = min(fm, min(leading_nonzero_fields(wa), leading_nonzero_fields(wb)));
-                        if (step < 21) {
-                            l = 21u * j + step;
-                            const int sh = 61 - 3 * step;
-                            c = (uint32_t)(wa >> sh) & 7u; rr = (uint32_t)(wb >> sh) & 7u;
-                            break;
-                        }
-                    }
-                    const uint32_t type = c < rr ? 0u : (c == rr ? 1u : 2u);
-                    const uint32_t lkey = type == 2u ? 255u - l : l;
-                    nk = ((uint64_t)(a - gs) << 24) | ((uint64_t)type << 22) | ((uint64_t)lkey << 14) | ((uint64_t)c << 11) | idx;
-                }
-                s_key[row] = nk;
-            }
-            __syncwarp();
-            // C: bitonic network with ascending comparators only (rows >= len act as +inf and never move)
-            uint64_t *key = s_key + gs;
-            for (uint32_t k = 2; k <= n2; k <<= 1) {
-                const uint32_t half = k >> 1;
-                for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
-                    const uint32_t i = ((t & ~(half - 1)) << 1) | (t & (half - 1));
-                    const uint32_t l = i ^ (k - 1);
-                    if (l < len) { const uint64_t x = key[i], y = key[l]; if (y < x) { key[i] = y; key[l] = x; } }
-                }
-                __syncwarp();
-                for (uint32_t jj = half >> 1; jj > 0; jj >>= 1) {
-                    for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
-                        const uint32_t i = ((t & ~(jj - 1)) << 1) | (t & (jj - 1));
-                        const uint32_t l = i | jj;
-                        if (l < len) { const uint64_t x = key[i], y = key[l]; if (y < x) { key[i] = y; key[l] = x; } }
-                    }
-                    __syncwarp();
-                }
-            }
-            // D: new runs, final LCPs
-            bool any = false;
-            uint32_t carry = gs;
-            for (uint32_t base = 0; base < len; base += 32) {
-                const uint32_t t = base + lane, row = gs + t;
-                const bool valid = t < len;
-                bool start = true, unres = false;
-                uint32_t newdepth = 0xFF;
-                if (valid && s_rdepth[row] != 0xFF) {
-                    const uint32_t olda = s_runa[row];
-                    const uint32_t kt = (uint32_t)(s_key[row] >> 11);
-                    const uint32_t c = kt & 7u, ty = (kt >> 11) & 3u, lk = (kt >> 3) & 255u;
-                    const uint32_t l = ty == 2u ? 255u - lk : lk;
-                    bool tiedprev = false;
-                    if (row > olda) {
-                        const uint32_t kp = (uint32_t)(s_key[row - 1] >> 11);
-                        tiedprev = kp == kt && c != 0;
-                        if (!tiedprev) {
-                            const uint32_t tp = (kp >> 11) & 3u, lp = (kp >> 3) & 255u;
-                            s_lcpout[row] = (uint8_t)min(l, tp == 2u ? 255u - lp : lp);
-                        }
-                    }
-                    const bool tiednext = t + 1 < len && s_runa[row + 1] == olda && s_rdepth[row + 1] != 0xFF &&
-                                          (uint32_t)(s_key[row + 1] >> 11) == kt && c != 0;
-                    start = !tiedprev;
-                    unres = tiedprev || tiednext;
-                    newdepth = l + 1;
-                }
-                const uint32_t bits = __ballot_sync(0xffffffffu, valid && start);
-                const uint32_t below = bits & (0xffffffffu >> (31 - lane));
-                const uint32_t anew = below ? gs + base + 31 - __clz(below) : carry;
-                __syncwarp();
-                if (valid) {
-                    s_runa[row] = (uint16_t)anew;
-                    s_rdepth[row] = unres ? (uint8_t)newdepth : (uint8_t)0xFF;
-                    if (start && unres) s_best[row] = 0;
-                }
-                if (bits) carry = gs + base + 31 - __clz(bits);
-                any |= unres;
-            }
-            __syncwarp();
-            if (!__any_sync(0xffffffffu, any)) break;
-        }
-        for (uint32_t t = lane; t < len; t += 32) s_sorted[gs + t] = (uint16_t)(gs + (uint32_t)(s_key[gs + t] & 0x7FFu));
+        if (len <= 32) order_group_regs<1>(gs, len, lane, W, s_words, s_len, s_best, s_sorted, s_lcpout);
+        else if (len <= 64) order_group_regs<2>(gs, len, lane, W, s_words, s_len, s_best, s_sorted, s_lcpout);
+        else order_group_smem(gs, len, lane, W, s_words, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
         __syncwarp();
     }
     __syncthreads();
@@ -489,7 +610,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         const uint32_t j = t0 + r;
         const uint32_t e = s_sorted[r];
         const uint32_t slot = slot_of(j);
-        if (A.SA) A.SA[slot] = s_pos[e];
+        if (A.SA) A.SA[slot] = A.pos[t0 + e];
         if (A.bwt) {
             const uint32_t pv = s_prev[e];
             const uint32_t c = pv & 7u;
@@ -502,7 +623,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
 
 static size_t group_tile_smem(int W)
 {
-    return (size_t)W * GT_S * 8 + (size_t)GT_S * 8 + (size_t)GT_S * 4 * 2 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 +
+    return (size_t)W * GT_S * 8 + (size_t)GT_S * 8 + (size_t)GT_S * 4 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 +
            (size_t)GT_GMAX * 2 * 2 + (size_t)GT_S * 3 + 16;
 }
 
@@ -648,7 +769,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     // ---- buffers
     const uint64_t ngroups = (N + 320 + 63) / 64;           // padded so windows past the end read zeros
     uint64_t *T3 = arena_alloc<uint64_t>(c, ngroups * 3 + 2);
-    uint8_t *Q = arena_alloc<uint8_t>(c, N + 16);
+    uint16_t *QL = arena_alloc<uint16_t>(c, N + 16);
     uint64_t *keyA = arena_alloc<uint64_t>(c, N), *keyB = arena_alloc<uint64_t>(c, N);
     uint32_t *posA = arena_alloc<uint32_t>(c, N), *posB = arena_alloc<uint32_t>(c, N);
     const uint32_t dcap = (uint32_t)(N / std::min<uint64_t>(GT_E, (uint64_t)c->opt_group_cap + 1) + 64);
@@ -662,7 +783,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         ProfScope ps(c, PC_PACK, 2 * total_bases + 2 * N + N + ngroups * 24, 2);
         BFQ_CUDA(cudaMemsetAsync(T3 + ngroups * 3, 0, 16, st));
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 16, div_up(nreads * 32, 256));
-        pack_reads_kernel<<<std::max(grid, 1), 256, 0, st>>>(d_bases, d_quals, d_off, nreads, lut, eos, T8, Q);
+        pack_reads_kernel<<<std::max(grid, 1), 256, 0, st>>>(d_bases, d_quals, d_off, nreads, lut, eos, T8, QL);
         pack3_kernel<<<div_up(ngroups, 256), 256, 0, st>>>(T8, N, ngroups, T3);
         BFQ_CUDA(cudaGetLastError());
     }
@@ -682,7 +803,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     auto words_for = [&](int depth) { return (int)std::max<int64_t>(0, ((int64_t)max_len - depth + 20) / 21); };
     GroupTileArgs G;
     memset(&G, 0, sizeof G);
-    G.T3 = T3; G.Q = Q; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
+    G.T3 = T3; G.QL = QL; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
     G.group_cap = (uint32_t)c->opt_group_cap;
 
