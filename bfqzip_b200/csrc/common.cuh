@@ -72,6 +72,8 @@ struct Arena {
 struct bfq_ctx {
     int device = 0;
     int num_sms = 148;
+    size_t l2_persist_max = 0;        // bytes of L2 that may be set aside for persisting lines
+    size_t l2_window_max = 0;         // largest access-policy window
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
     bfq::Arena arena;

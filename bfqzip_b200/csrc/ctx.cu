@@ -154,6 +154,8 @@ int bfq_ctx_create(bfq_ctx **out, int device)
             return BFQ_ENODEVICE;
         }
         c->num_sms = prop.multiProcessorCount;
+        c->l2_persist_max = prop.persistingL2CacheMaxSize > 0 ? (size_t)prop.persistingL2CacheMaxSize : 0;
+        c->l2_window_max = prop.accessPolicyMaxWindowSize > 0 ? (size_t)prop.accessPolicyMaxWindowSize : 0;
         BFQ_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
         c->stream = c->own_stream;
         BFQ_CUDA(cudaMallocHost(&c->h_small, 4096));

@@ -138,15 +138,19 @@ __device__ __forceinline__ uint32_t sym_code(const uint64_t *__restrict__ T3, ui
 // ============================================================================ initial keys
 template <typename K>
 __global__ void __launch_bounds__(256)
-init_keys_kernel(const uint64_t *__restrict__ T3, uint32_t n, int k, K *__restrict__ keys,
-                 uint32_t *__restrict__ vals)
+init_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k,
+                 K *__restrict__ keys, uint32_t *__restrict__ vals)
 {
     const uint32_t p = blockIdx.x * 256u + threadIdx.x;
     if (p >= n) return;
     uint64_t w = text_window(T3, p);
     int f = leading_nonzero_fields(w);          // symbols before the first terminator
     if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
-    keys[p] = (K)(w >> (64 - 3 * k));
+    // bits above the k symbols are not sorted on: QL[p] rides along there (k <= 16), so the group
+    // kernel gets the previous quality and the suffix length with the sequentially read key
+    uint64_t key = w >> (64 - 3 * k);
+    if (QL) key |= (uint64_t)QL[p] << 48;
+    keys[p] = (K)key;
     vals[p] = p;
 }
 
@@ -192,6 +196,8 @@ struct GroupTileArgs {
     uint32_t *defer_count;      // [0] groups deferred, [1] members (filled by defer_len_kernel)
     uint32_t *defer_start;      // list index of the head of every deferred group
     uint32_t defer_cap;
+    uint64_t kmask;             // key bits that take part in group equality (level 0: the 3*ksym symbol bits)
+    int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
 };
 
@@ -501,7 +507,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         const uint64_t j = (uint64_t)t0 + r;
         bool h = true;                                    // slots past the list end count as heads
         if (r <= GT_S && j < m && j > 0) {
-            const K kc = keys[j], kp = keys[j - 1];
+            const K kc = __ldcs(&keys[j]) & (K)A.kmask, kp = __ldcs(&keys[j - 1]) & (K)A.kmask;
             h = (kc != kp) || ((kc & (K)7) == 0);
         }
         const uint32_t bits = __ballot_sync(0xffffffffu, h);
@@ -543,7 +549,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                         bool write = true; uint32_t l = 0;
                         if (j == 0) write = A.level0;
                         else {
-                            const K kc = keys[j], kp = keys[j - 1];
+                            const K kc = keys[j] & (K)A.kmask, kp = keys[j - 1] & (K)A.kmask;
                             if (!A.level0 && ((uint64_t)kc >> kshift) != ((uint64_t)kp >> kshift)) write = false;   // written one level up
                             else l = A.depth0 + head_lcp<K>(kp, kc, ksym);
                         }
@@ -561,9 +567,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                 }
                 if (fits) {
                     gs16 = (uint16_t)gs;
-                    const uint32_t p = A.pos[j];
+                    const uint32_t p = __ldcs(&A.pos[j]);
                     s_sorted[r] = (uint16_t)r;
-                    const uint32_t ql = A.QL[p];
+                    const uint32_t ql = A.embed ? (uint32_t)((uint64_t)keys[j] >> 48) : (uint32_t)A.QL[p];
                     if (A.bwt) {
                         const uint32_t c = p > 0 ? sym_code(A.T3, (uint64_t)p - 1) : 0u;
                         s_prev[r] = (uint16_t)(c | ((c ? (ql & 255u) : (uint32_t)A.eos) << 8));
@@ -614,9 +620,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         if (A.bwt) {
             const uint32_t pv = s_prev[e];
             const uint32_t c = pv & 7u;
-            A.bwt[slot] = c ? (uint8_t)(A.code2byte >> (8 * c)) : A.eos;
-            A.qs[slot] = (uint8_t)(pv >> 8);
-            if ((uint32_t)r != gs) A.lcp[slot] = (uint8_t)(depth + s_lcpout[r]);
+            __stcs(&A.bwt[slot], c ? (uint8_t)(A.code2byte >> (8 * c)) : A.eos);
+            __stcs(&A.qs[slot], (uint8_t)(pv >> 8));
+            if ((uint32_t)r != gs) __stcs(&A.lcp[slot], (uint8_t)(depth + s_lcpout[r]));
         }
     }
 }
@@ -640,7 +646,7 @@ __device__ __forceinline__ uint64_t cut_key(const uint64_t *__restrict__ T3, uin
 // one warp per deferred group: its length (distance to the next head) and the SA slot of its head
 template <typename K>
 __global__ void __launch_bounds__(256)
-defer_len_kernel(const K *__restrict__ keys, uint32_t m, int level0, int kshift,
+defer_len_kernel(const K *__restrict__ keys, K kmask, uint32_t m, int level0, int kshift,
                  const uint32_t *__restrict__ g_slot, const uint32_t *__restrict__ g_off,
                  const uint32_t *__restrict__ dstart, uint32_t G, uint32_t *__restrict__ dlen,
                  uint32_t *__restrict__ dslot)
@@ -653,7 +659,7 @@ defer_len_kernel(const K *__restrict__ keys, uint32_t m, int level0, int kshift,
     for (uint64_t base = (uint64_t)start + 1; base < m; base += 32) {
         const uint64_t j = base + lane;
         bool h = false;
-        if (j < m) { const K kc = keys[j], kp = keys[j - 1]; h = (kc != kp) || ((kc & (K)7) == 0); }
+        if (j < m) { const K kc = keys[j] & kmask, kp = keys[j - 1] & kmask; h = (kc != kp) || ((kc & (K)7) == 0); }
         const uint32_t b = __ballot_sync(0xffffffffu, h);
         if (b) { end = (uint32_t)base + __ffs(b) - 1; break; }
     }
@@ -794,11 +800,39 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     k = std::min(k, 21);
     {
         ProfScope ps(c, PC_KEYS, N * (8 + 4) + ngroups * 24);
-        init_keys_kernel<uint64_t><<<div_up(N, 256), 256, 0, st>>>(T3, (uint32_t)N, k, keyA, posA);
+        init_keys_kernel<uint64_t><<<div_up(N, 256), 256, 0, st>>>(T3, k <= 16 ? QL : nullptr, (uint32_t)N, k, keyA, posA);
     }
     int flip = radix_sort_pairs64(c, keyA, keyB, posA, posB, N, 3 * k);
     uint64_t *keys = flip ? keyB : keyA, *keys_alt = flip ? keyA : keyB;
     uint32_t *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
+
+    // The packed text is what every group gathers from at random: pin it in L2 (persisting access
+    // window, set aside only for the group kernels) while the sorted list streams through; T3 of config 2 is 38 MB of the 126 MB L2.
+    const size_t t3_bytes = (ngroups * 3 + 2) * 8;
+    bool pinned = false;
+    if (c->l2_persist_max > 0 && c->l2_window_max > 0 &&
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min(c->l2_persist_max, t3_bytes + (t3_bytes >> 3))) == cudaSuccess) {
+        cudaStreamAttrValue av;
+        memset(&av, 0, sizeof av);
+        av.accessPolicyWindow.base_ptr = T3;
+        av.accessPolicyWindow.num_bytes = std::min(t3_bytes, c->l2_window_max);
+        av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)std::min(c->l2_persist_max, t3_bytes + (t3_bytes >> 3)) / (double)av.accessPolicyWindow.num_bytes);
+        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        pinned = cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+        if (!pinned) cudaGetLastError();
+    }
+    struct Unpin {
+        cudaStream_t st; bool on;
+        ~Unpin() {
+            if (!on) return;
+            cudaStreamAttrValue av;
+            memset(&av, 0, sizeof av);
+            cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
+            cudaCtxResetPersistingL2Cache();
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0);   // give the set-aside back to parts B and C
+        }
+    } unpin{st, pinned};
 
     auto words_for = [&](int depth) { return (int)std::max<int64_t>(0, ((int64_t)max_len - depth + 20) / 21); };
     GroupTileArgs G;
@@ -813,6 +847,8 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         BFQ_CUDA(cudaMemsetAsync(dcount, 0, 16, st));
         G.pos = pos; G.m = m; G.level0 = level == 0; G.ksym = ksym; G.depth0 = depth;
         G.W = words_for(depth + ksym);
+        G.kmask = level == 0 ? ((1ull << (3 * ksym)) - 1) : ~0ull;
+        G.embed = level == 0 && ksym <= 16;
         G.g_slot = level ? dtab[parity ^ 1][2] : nullptr;
         G.g_off = level ? dtab[parity ^ 1][3] : nullptr;
         G.defer_start = dtab[parity][0];
@@ -828,7 +864,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         {
             ProfScope ps(c, PC_DEFER, 0, 2);
             defer_len_kernel<uint64_t><<<div_up((uint64_t)ndef * 32, 256), 256, 0, st>>>(
-                keys, m, G.level0, 3 * ksym, G.g_slot, G.g_off, dstart, ndef, dlen, dslot);
+                keys, G.kmask, m, G.level0, 3 * ksym, G.g_slot, G.g_off, dstart, ndef, dlen, dslot);
             scan_excl_u32_kernel<<<1, 1024, 0, st>>>(dlen, doff, ndef, dcount + 1);
             BFQ_CUDA(cudaGetLastError());
         }
