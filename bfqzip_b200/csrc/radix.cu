@@ -48,27 +48,32 @@ template <typename K>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_hist_kernel(const K *__restrict__ keys, uint64_t n, RsPasses P, uint32_t *__restrict__ hist)
 {
-    __shared__ uint32_t sh[RS_MAX_PASSES][RS_RADIX];
-    for (int i = threadIdx.x; i < RS_MAX_PASSES * RS_RADIX; i += RS_THREADS) (&sh[0][0])[i] = 0;
+    // Two shared copies of the per-pass histograms (even / odd warps) halve same-address collisions;
+    // a warp whose 32 digits are all equal (constant high bits) adds once instead of 32 times.
+    __shared__ uint32_t sh[2][RS_MAX_PASSES][RS_RADIX];
+    for (int i = threadIdx.x; i < 2 * RS_MAX_PASSES * RS_RADIX; i += RS_THREADS) (&sh[0][0][0])[i] = 0;
     __syncthreads();
+    const int lane = threadIdx.x & 31, copy = (threadIdx.x >> 5) & 1;
     const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
     for (uint64_t base = (uint64_t)blockIdx.x * RS_THREADS; base < n; base += stride) {
         const uint64_t i = base + threadIdx.x;          // block-uniform trip count
         const bool ok = i < n;
-        K k = ok ? keys[i] : (K)0;
+        const K k = ok ? keys[i] : (K)0;
 #pragma unroll
         for (int p = 0; p < RS_MAX_PASSES; p++) {
             if (p < P.num) {
-                uint32_t d = ok ? digit_of(k, P.shift[p], (1u << P.bits[p]) - 1) : 0xffffffffu;
-                // warp-aggregated: one shared atomic per distinct digit in the warp
-                uint32_t m = __match_any_sync(0xffffffffu, d);
-                if (ok && (__ffs(m) - 1) == (int)(threadIdx.x & 31)) atomicAdd(&sh[p][d], __popc(m));
+                const uint32_t d = digit_of(k, P.shift[p], (1u << P.bits[p]) - 1);
+                const uint32_t d0 = __shfl_sync(0xffffffffu, d, 0);
+                const uint32_t same = __ballot_sync(0xffffffffu, ok && d == d0);
+                const uint32_t act = __ballot_sync(0xffffffffu, ok);
+                if (same == act) { if (lane == 0 && act) atomicAdd(&sh[copy][p][d0], __popc(act)); }
+                else if (ok) atomicAdd(&sh[copy][p][d], 1u);
             }
         }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < P.num * RS_RADIX; i += RS_THREADS) {
-        uint32_t v = (&sh[0][0])[i];
+        const uint32_t v = (&sh[0][0][0])[i] + (&sh[1][0][0])[i];
         if (v) atomicAdd(&hist[i], v);
     }
 }
@@ -105,7 +110,7 @@ template <typename S> __device__ __forceinline__ void st_status(S *p, S v)
 }
 
 template <typename K, typename S, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
                    const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out,
                    uint32_t n, int shift, int bits, const uint32_t *__restrict__ digit_base,
@@ -121,6 +126,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     __shared__ uint32_t digit_gbase[RS_RADIX];
     __shared__ uint32_t warp_tot[RS_WARPS];
     __shared__ K stage[TILE];
+    __shared__ uint8_t s_dig[TILE];              // digit of the key staged at each slot (for the payload pass)
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t mask = (1u << bits) - 1;
@@ -216,15 +222,14 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     }
     __syncthreads();
 
-    // ---- coalesced output of keys; remember each slot's global index for the payload
-    uint32_t gidx[ITEMS];
+    // ---- coalesced output of keys; keep each slot's digit for the payload pass
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t slot = i * RS_THREADS + tid;
         K k = stage[slot];
         uint32_t d = digit_of(k, shift, mask);
-        gidx[i] = digit_gbase[d] + slot;
-        if (slot < valid) keys_out[gidx[i]] = k;
+        s_dig[slot] = (uint8_t)d;
+        if (slot < valid) keys_out[digit_gbase[d] + slot] = k;
     }
     __syncthreads();
 
@@ -240,7 +245,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t slot = i * RS_THREADS + tid;
-        if (slot < valid) vals_out[gidx[i]] = stage32[slot];
+        if (slot < valid) vals_out[digit_gbase[s_dig[slot]] + slot] = stage32[slot];
     }
 }
 
