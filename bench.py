@@ -11,8 +11,9 @@ like BFQzip_parallel.py; no data-path collective) -> weak scaling.
 `value`  : device-resident inputs/outputs (bfq_pipeline_dev), CUDA events on the launching stream.
 `e2e`    : the same metric through the host-buffer C ABI call (bfq_pipeline) with pinned host
            buffers; H2D of the reads and D2H of .bwt/.bwt.qs/.1.lcp + rebuilt reads inside the timing.
-`roofline`: dominant kernel class = the radix-sort pass (rs_onesweep_kernel); achieved = its
-           algorithmic bytes (2*(8+4) B per sorted element) / its CUDA-event time inside the timed steps.
+`roofline`: the kernel class with the largest share of the timed steps (CUDA events around every launch
+           of every class); achieved = that class's algorithmic bytes / its time.
+           `roofline_all` lists the same figure for every class (the sort pass and the scans included).
 `cpu_baseline` / --impl reference: the UNMODIFIED reference (oracle/_ref: gsufsort + bfq_ext) on the
            host cores, on a bounded sample of the same workload.
 """
@@ -242,8 +243,20 @@ def gpu_arm(args):
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
-        rp_ms, rp_n, rp_bytes = prof["radix_pass"]
-        achieved = (rp_bytes / 1e9) / (rp_ms * 1e-3) if rp_ms > 0 else 0.0
+        KNAME = {"radix_pass": "rs_onesweep_kernel", "radix_hist": "rs_hist_kernel", "pack": "pack_reads_kernel+pack3_kernel",
+                 "keys": "init_keys_kernel", "group": "group_tile_kernel", "defer": "defer_*_kernel", "hist": "hist256_kernel",
+                 "rank": "rank_*_kernel", "cluster": "cluster_tile_kernel", "cluster_long": "cluster_long_kernel",
+                 "rule11": "rule11_kernel", "walk": "walk_kernel", "assemble": "assemble_kernel"}
+        TRAFFIC = {"group": 1782.1e6, "radix_pass": None}     # ncu dram read+write per launch (profiles/), where captured
+        roof_all = {}
+        for k, (k_ms, k_n, k_bytes) in prof.items():
+            if k_ms > 0 and k_n:
+                roof_all[k] = {"kernel": KNAME[k], "ms_per_step": k_ms / args.steps, "launches_per_step": k_n / args.steps,
+                               "achieved": (k_bytes / 1e9) / (k_ms * 1e-3), "frac": (k_bytes / 1e9) / (k_ms * 1e-3) / peak,
+                               "share_of_step": k_ms / ms}
+        dom = max(roof_all, key=lambda k: roof_all[k]["ms_per_step"])
+        rp_ms, rp_n, rp_bytes = prof[dom]
+        achieved = roof_all[dom]["achieved"]
         # CPU baseline on a bounded sample (rank 0, N=1 only)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -267,10 +280,11 @@ def gpu_arm(args):
             "e2e": {"value": e2e_val, "unit": "Gbases/s", "h2d_bytes_per_step": int(2 * total + 8 * (nreads + 1)),
                     "d2h_bytes_per_step": int(3 * N + 2 * total), "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "rs_onesweep_kernel (radix_pass)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": f"{KNAME[dom]} ({dom})", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": TRAFFIC.get(dom),
                          "peak_source": peak_src, "launches": rp_n, "avg_launch_ms": rp_ms / rp_n if rp_n else None,
                          "share_of_step": rp_ms / ms if ms else None},
+            "roofline_all": roof_all,
             "stages_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
             "cpu_baseline": cpu,
             "clocks": sampler.summary(),

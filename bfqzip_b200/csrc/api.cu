@@ -86,7 +86,7 @@ static void remember(bfq_ctx *c, const SmoothResult &S)
 static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
                          uint64_t nreads, uint64_t total_bases, const bfq_params *P, uint8_t *d_bwt,
                          uint8_t *d_qs, uint8_t *d_lcp, uint8_t *d_out_bases, uint8_t *d_out_quals,
-                         bfq_stats *stats)
+                         bfq_stats *stats, uint8_t *h_bwt = nullptr, uint8_t *h_qs = nullptr, uint8_t *h_lcp = nullptr)
 {
     uint64_t mn, mx;
     check_reads_dev(c, d_off, nreads, total_bases, &mn, &mx);
@@ -101,6 +101,15 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
         build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, P->eos_byte, d_bwt, d_qs, d_lcp, nullptr);
         c->arena.release(mk);        // sort scratch is dead (stream-ordered) once the gather is queued
     }
+    if (h_bwt || h_qs || h_lcp) {
+        // the three files are final: copy them out on the side stream while parts B and C run
+        BFQ_CUDA(cudaEventRecord(c->ev_a, c->stream));
+        BFQ_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_a, 0));
+        if (h_bwt) BFQ_CUDA(cudaMemcpyAsync(h_bwt, d_bwt, N, cudaMemcpyDeviceToHost, c->copy_stream));
+        if (h_qs) BFQ_CUDA(cudaMemcpyAsync(h_qs, d_qs, N, cudaMemcpyDeviceToHost, c->copy_stream));
+        if (h_lcp) BFQ_CUDA(cudaMemcpyAsync(h_lcp, d_lcp, N, cudaMemcpyDeviceToHost, c->copy_stream));
+        BFQ_CUDA(cudaEventRecord(c->ev_copy, c->copy_stream));
+    }
     SmoothResult S;
     smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats);
     if (S.nreads != nreads) BFQ_FAIL(BFQ_ECUDA, "internal error: %llu end-markers for %llu reads", (unsigned long long)S.nreads, (unsigned long long)nreads);
@@ -111,6 +120,7 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
         uint64_t *d_oo = arena_alloc<uint64_t>(c, nreads + 1);
         rebuild_dev(c, S, P, nullptr, d_out_bases, d_out_quals, d_oo, nullptr);
     }
+    if (h_bwt || h_qs || h_lcp) BFQ_CUDA(cudaStreamWaitEvent(c->stream, c->ev_copy, 0));   // side copies join the main stream
     BFQ_CUDA(cudaStreamSynchronize(c->stream));
     remember(c, S);
 }
@@ -120,7 +130,7 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
 using namespace bfq;
 
 #define API_BEGIN try { begin_call(ctx);
-#define API_END   return BFQ_OK; } catch (bfq::Error &e__) { if (ctx) cudaStreamSynchronize(ctx->stream); cudaGetLastError(); return e__.code; } \
+#define API_END   return BFQ_OK; } catch (bfq::Error &e__) { if (ctx) { cudaStreamSynchronize(ctx->stream); if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream); } cudaGetLastError(); return e__.code; } \
                   catch (std::exception &ex__) { bfq::set_error("exception: %s", ex__.what()); return BFQ_ENOMEM; }
 
 static uint64_t host_check_off(const uint64_t *off, uint64_t nreads, uint64_t *max_len = nullptr)
@@ -204,10 +214,7 @@ int bfq_pipeline(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const
     uint64_t *d_o = to_device(ctx, off, nreads + 1);
     uint8_t *d_bwt = arena_alloc<uint8_t>(ctx, N + 64), *d_qs = arena_alloc<uint8_t>(ctx, N + 64), *d_lcp = arena_alloc<uint8_t>(ctx, N + 64);
     uint8_t *d_ob = arena_alloc<uint8_t>(ctx, total + 64), *d_oq = arena_alloc<uint8_t>(ctx, total + 64);
-    pipeline_dev(ctx, d_b, d_q, d_o, nreads, total, params, d_bwt, d_qs, d_lcp, d_ob, d_oq, stats);
-    if (bwt) BFQ_CUDA(cudaMemcpyAsync(bwt, d_bwt, N, cudaMemcpyDeviceToHost, ctx->stream));
-    if (qs) BFQ_CUDA(cudaMemcpyAsync(qs, d_qs, N, cudaMemcpyDeviceToHost, ctx->stream));
-    if (lcp) BFQ_CUDA(cudaMemcpyAsync(lcp, d_lcp, N, cudaMemcpyDeviceToHost, ctx->stream));
+    pipeline_dev(ctx, d_b, d_q, d_o, nreads, total, params, d_bwt, d_qs, d_lcp, d_ob, d_oq, stats, bwt, qs, lcp);
     BFQ_CUDA(cudaMemcpyAsync(out_bases, d_ob, total, cudaMemcpyDeviceToHost, ctx->stream));
     BFQ_CUDA(cudaMemcpyAsync(out_quals, d_oq, total, cudaMemcpyDeviceToHost, ctx->stream));
     BFQ_CUDA(cudaStreamSynchronize(ctx->stream));

@@ -76,6 +76,8 @@ struct bfq_ctx {
     size_t l2_window_max = 0;         // largest access-policy window
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // D2H of the part-A files overlaps parts B and C
+    cudaEvent_t ev_a = nullptr, ev_copy = nullptr;
     bfq::Arena arena;
     // host pinned scratch for small read-backs
     uint64_t *h_small = nullptr;      // 4 KiB pinned

@@ -158,6 +158,9 @@ int bfq_ctx_create(bfq_ctx **out, int device)
         c->l2_window_max = prop.accessPolicyMaxWindowSize > 0 ? (size_t)prop.accessPolicyMaxWindowSize : 0;
         BFQ_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
         c->stream = c->own_stream;
+        BFQ_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        BFQ_CUDA(cudaEventCreateWithFlags(&c->ev_a, cudaEventDisableTiming));
+        BFQ_CUDA(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
         BFQ_CUDA(cudaMallocHost(&c->h_small, 4096));
         BFQ_CUDA(cudaMalloc(&c->d_small, 4096));
     } catch (Error &er) {
@@ -178,6 +181,9 @@ void bfq_ctx_destroy(bfq_ctx *c)
     c->arena.destroy();
     if (c->h_small) cudaFreeHost(c->h_small);
     if (c->d_small) cudaFree(c->d_small);
+    if (c->ev_a) cudaEventDestroy(c->ev_a);
+    if (c->ev_copy) cudaEventDestroy(c->ev_copy);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
 }

@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--B", type=int, default=0)
     ap.add_argument("--seed", type=int, default=1001)
     ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--opt", action="append", default=[], help="ctx option key=value (repeatable)")
     ap.add_argument("--stages", action="store_true", help="print the per-stage CUDA-event times")
     a = ap.parse_args()
 
@@ -35,6 +36,9 @@ def main():
     g = lib.BfqGpu(a.M, a.B, 0)
     if a.stages:
         g.set_option("profile", 1)
+    for kv in a.opt:
+        k, v = kv.split("=")
+        g.set_option(k, int(v))
     P = lib.default_params(eos=0)
     d_b = torch.from_numpy(bases).to(dev); d_q = torch.from_numpy(quals).to(dev)
     d_off = torch.from_numpy(off.view(np.int64)).to(dev)
