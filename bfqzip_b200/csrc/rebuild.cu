@@ -28,6 +28,12 @@ walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase
     uint64_t wpos;            // next write index
     if (off_known) wpos = off_known[g + 1];
     else wpos = (uint64_t)g * (uint32_t)max_len;
+    // Known lengths: the read is written backwards into its final place.  Bytes are gathered in two
+    // 8-byte shift registers and leave as one aligned 64-bit store per 8 symbols (single-byte stores
+    // scattered over the kernel's lifetime cost a 32-byte read-modify-write in DRAM each).
+    uint64_t accb = 0, accq = 0;
+    int cnt = 0;
+    const bool wide = ((reinterpret_cast<uintptr_t>(out_b) | reinterpret_cast<uintptr_t>(out_q)) & 7) == 0;
     int k = 0;
     for (; k < max_len; k++) {
         const uint8_t *L = lines + (row >> 5) * 64;
@@ -40,12 +46,27 @@ walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase
         const uint8_t q = L[32 + r];
         uint8_t base = (uint8_t)(code2byte >> (8 * c));
         if (q & 0x80) base = obase[row];                     // noise-reduced row (BWT_MOD, bfq_ext.cpp:555)
-        if (off_known) { wpos--; out_b[wpos] = base; out_q[wpos] = q & 0x7F; }
-        else { out_b[wpos] = base; out_q[wpos] = q & 0x7F; wpos++; }
+        if (off_known) {
+            wpos--;
+            accb = (accb << 8) | base;
+            accq = (accq << 8) | (uint64_t)(q & 0x7F);
+            cnt++;
+            if ((wpos & 7) == 0 || !wide) {
+                if (cnt == 8) {
+                    *reinterpret_cast<uint64_t *>(out_b + wpos) = accb;
+                    *reinterpret_cast<uint64_t *>(out_q + wpos) = accq;
+                } else {
+                    for (int t = 0; t < cnt; t++) { out_b[wpos + t] = (uint8_t)(accb >> (8 * t)); out_q[wpos + t] = (uint8_t)(accq >> (8 * t)); }
+                }
+                cnt = 0;
+            }
+        } else { out_b[wpos] = base; out_q[wpos] = q & 0x7F; wpos++; }
         const uint32_t mm = ((c & 1) ? p0 : ~p0) & ((c & 2) ? p1 : ~p1) & ((c & 4) ? p2 : ~p2);
-        const uint32_t cnt = c == 1 ? a.x : c == 2 ? a.y : c == 3 ? a.z : c == 4 ? a.w : b.x;
-        row = (uint64_t)cnt + __popc(mm & ((1u << r) - 1u));
+        const uint32_t cntc = c == 1 ? a.x : c == 2 ? a.y : c == 3 ? a.z : c == 4 ? a.w : b.x;
+        row = (uint64_t)cntc + __popc(mm & ((1u << r) - 1u));
     }
+    if (off_known)
+        for (int t = 0; t < cnt; t++) { out_b[wpos + t] = (uint8_t)(accb >> (8 * t)); out_q[wpos + t] = (uint8_t)(accq >> (8 * t)); }
     if (lens) lens[g] = (uint32_t)k;
 }
 

@@ -330,6 +330,8 @@ struct SmoothLists {
 // flagged rows (those belong to a cluster that started in an earlier tile, whose owner writes them).
 constexpr int CL_THREADS = 256;
 constexpr int CL_TILE = 4096;
+constexpr int CL_EXT = 512;                 // rows staged past the tile: a cluster that starts in the tile and ends inside
+constexpr int CL_S = CL_TILE + CL_EXT;      // the staged window is finished here, longer ones go to cluster_long_kernel
 
 __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stats, unsigned long long *g_stats)
 {
@@ -351,9 +353,10 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
                     uint8_t *__restrict__ obase, SmoothLists L)
 {
-    __shared__ uint8_t s_lcp[CL_TILE + 8];      // s_lcp[r + 1] = lcp[t0 + r], r = -1 .. CL_TILE + 1
-    __shared__ uint8_t s_code[CL_TILE];
-    __shared__ uint8_t s_q[CL_TILE];
+    __shared__ uint8_t s_lcp[CL_S + 8];         // s_lcp[r + 1] = lcp[t0 + r], r = -1 .. CL_S + 1
+    __shared__ uint8_t s_code[CL_S];
+    __shared__ uint8_t s_q[CL_S];
+    __shared__ uint8_t s_f[CL_S + 4];           // rule 5-6 flag of every staged row (+ one past the window)
     __shared__ uint16_t s_starts[CL_TILE / 2 + 2];
     __shared__ uint32_t s_nstarts, s_lead;
     __shared__ uint8_t s_lut[256];
@@ -366,65 +369,56 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     if (tid == 0) { s_nstarts = 0; s_lead = CL_TILE; }
     if (tid < ST_COUNT) s_stats[tid] = 0;
     __syncthreads();
-    for (int r = tid; r < CL_TILE + 3; r += CL_THREADS) {
+    for (int r = tid; r < CL_S + 3; r += CL_THREADS) {
         int64_t i = t0 + r - 1;
         s_lcp[r] = (i >= 0 && i < nn) ? lcp[i] : 0;
     }
-    for (int r = tid; r < CL_TILE; r += CL_THREADS) {
+    for (int r = tid; r < CL_S; r += CL_THREADS) {
         int64_t i = t0 + r;
         bool ok = i < nn;
         s_code[r] = ok ? s_lut[bwt[i]] : 0;
         s_q[r] = ok ? qs[i] : 0;
     }
     __syncthreads();
-
-    auto lcp_at = [&](int64_t i) -> int {
-        if (i < 0 || i >= nn) return 0;
-        int64_t r = i - t0 + 1;
-        if (r >= 0 && r < CL_TILE + 3) return s_lcp[r];
-        return lcp[i];
-    };
-    auto F = [&](int64_t i) -> bool {
-        if (i <= 0 || i >= nn) return false;
-        return f_flag(lcp_at(i - 1), lcp_at(i), lcp_at(i + 1), false, i == nn - 1);
-    };
+    // flags of rows t0 .. t0 + CL_S (the last one only tells whether a cluster ends inside the window)
+    for (int r = tid; r <= CL_S; r += CL_THREADS) {
+        int64_t i = t0 + r;
+        bool f = false;
+        if (i > 0 && i < nn) f = f_flag(s_lcp[r], s_lcp[r + 1], s_lcp[r + 2], false, i == nn - 1);
+        s_f[r] = f;
+    }
+    __syncthreads();
 
     // ---- cluster starts and the leading run
     for (int r = tid; r < CL_TILE; r += CL_THREADS) {
-        int64_t i = t0 + r;
-        if (i >= nn) break;
-        bool fi = F(i);
-        if (!fi) {
+        if (t0 + r >= nn) break;
+        if (!s_f[r]) {
             atomicMin(&s_lead, (uint32_t)r);
-            if (F(i + 1)) s_starts[atomicAdd(&s_nstarts, 1u)] = (uint16_t)r;
+            if (s_f[r + 1]) s_starts[atomicAdd(&s_nstarts, 1u)] = (uint16_t)r;
         }
     }
     __syncthreads();
     const uint32_t nstarts = s_nstarts;
-    const uint32_t long_len = g_sc.long_len;
     uint32_t st[ST_COUNT];
 #pragma unroll
     for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
 
     for (uint32_t idx = tid; idx < nstarts; idx += CL_THREADS) {
-        const int64_t a = t0 + s_starts[idx];
-        int64_t e = a + 1;
-        while ((uint64_t)(e - a) <= long_len && F(e)) e++;
-        const uint32_t len = (uint32_t)(e - a);
-        if (len > long_len) {                                  // still open: hand over
+        const int a = s_starts[idx];
+        int e = a + 1;
+        while (e <= CL_S && s_f[e]) e++;
+        if (e > CL_S || (uint32_t)(e - a) > g_sc.long_len) {    // open at the end of the window, or too long for one thread: hand over
             uint32_t k = atomicAdd(L.long_count, 1u);
-            if (k < L.long_cap) L.long_starts[k] = (uint32_t)a;
+            if (k < L.long_cap) L.long_starts[k] = (uint32_t)(t0 + a);
             continue;
         }
-        const int64_t tile_end = t0 + CL_TILE;
+        const uint32_t len = (uint32_t)(e - a);
         // pass 1: statistics (rule 8)
-        unsigned long long fpack = 0;                          // 12-bit counters per code (len < 4096)
+        unsigned long long fpack = 0;                          // 12-bit counters per code (len <= long_len <= 4000)
         ClAcc acc;
         acc.hiq = 0; acc.base_num = 0; acc.mx = 0; acc.isum = 0; acc.dsum = 0.0;
-        for (int64_t i = a; i < e; i++) {
-            uint32_t c; uint8_t q;
-            if (i < tile_end) { c = s_code[i - t0]; q = s_q[i - t0]; }
-            else { c = s_lut[bwt[i]]; q = qs[i]; }
+        for (int r = a; r < e; r++) {
+            const uint32_t c = s_code[r]; const uint8_t q = s_q[r];
             if (c) {
                 fpack += 1ull << (12 * (c - 1));
                 acc.base_num++;
@@ -445,21 +439,18 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
         if (d.act == ACT_RULE11) {
             uint32_t k = atomicAdd(L.r11_count, 1u);
             if (k < L.r11_cap)
-                L.r11[k] = R11Desc{(uint32_t)a, len, d.f0 | (d.f1 << 8) | ((uint32_t)d.newqs << 16) | (acc.hiq << 24), 0};
+                L.r11[k] = R11Desc{(uint32_t)(t0 + a), len, d.f0 | (d.f1 << 8) | ((uint32_t)d.newqs << 16) | (acc.hiq << 24), 0};
         }
-        if (d.act != ACT_RULE10 && e <= tile_end) continue;     // nothing changes, all rows in tile
-        // pass 2: apply rule 10 / write the rows that lie beyond this tile
+        if (d.act != ACT_RULE10 && e <= CL_TILE) continue;     // nothing changes, all rows inside the tile
+        // pass 2: apply rule 10 / write the rows that lie beyond this tile (the next tile skips them)
         const uint8_t symb = g_sc.code2byte[d.sym];
-        for (int64_t i = a; i < e; i++) {
-            const bool in_tile = i < tile_end;
-            uint32_t c; uint8_t q;
-            if (in_tile) { c = s_code[i - t0]; q = s_q[i - t0]; }
-            else { c = s_lut[bwt[i]]; q = qs[i]; }
+        for (int r = a; r < e; r++) {
+            const uint32_t c = s_code[r]; const uint8_t q = s_q[r];
             uint8_t o = q;
             if (d.act == ACT_RULE10) o = rule10_row(c, q, d.sym, acc.hiq, d.newqs, st);
-            if (o & 0x80) obase[i] = symb;
-            if (in_tile) { if (o != q) s_q[i - t0] = o; }
-            else *line_q(lines, (uint64_t)i) = store_q(o);
+            if (o & 0x80) obase[t0 + r] = symb;
+            if (r < CL_TILE) { if (o != q) s_q[r] = o; }
+            else *line_q(lines, (uint64_t)(t0 + r)) = store_q(o);
         }
     }
     __syncthreads();
