@@ -161,6 +161,7 @@ def gpu_arm(args):
         raise SystemExit("bench.py: no CUDA device; this benchmark has no CPU fallback for the product arm")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"        # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     W = WORKLOAD
     M, B = W["M"], W["B"]
