@@ -235,22 +235,25 @@ __device__ __forceinline__ uint32_t head_lcp(K kprev, K kcur, int ksym)
 // data: most members are prefixes of the longest one and a single iteration resolves the group.
 struct RefCmp { uint32_t l, c, r; };
 
-__device__ __forceinline__ RefCmp ref_compare(const uint64_t *s_words, const uint8_t *s_len, int W,
-                                              uint32_t mem, uint32_t ref, uint32_t D)
+__device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, const uint32_t *s_pos, const uint8_t *s_len,
+                                              int depth, uint32_t mem, uint32_t ref, uint32_t D)
 {
+    // The strings are read straight from the packed text (L1 / pinned L2): a member is compared once per
+    // iteration, so staging it in shared memory would cost more than it saves (and occupancy with it).
     const uint32_t lm = s_len[mem], lr = s_len[ref];
     const uint32_t lmin = min(lm, lr);
+    const uint64_t pm = (uint64_t)s_pos[mem] + depth, pr = (uint64_t)s_pos[ref] + depth;
     RefCmp o;
     o.l = lmin;
-    const int jend = min(W, (int)(lmin / 21u) + 1);      // a difference cannot lie past the shorter string's terminator
-    for (int j = (int)(D / 21u); j < jend; j++) {
-        const uint64_t x = s_words[j * GT_S + mem] ^ s_words[j * GT_S + ref];
-        if (x) { o.l = min(lmin, 21u * j + (uint32_t)(__clzll((long long)x) / 3)); break; }
+    if (mem != ref) {
+        const uint32_t jend = (lmin + 20u) / 21u;         // a difference cannot lie past the shorter string's terminator
+        for (uint32_t j = D / 21u; j < jend; j++) {
+            const uint64_t x = text_window(T3, pm + 21u * j) ^ text_window(T3, pr + 21u * j);
+            if (x) { o.l = min(lmin, 21u * j + (uint32_t)(__clzll((long long)x) / 3)); break; }
+        }
     }
-    const uint32_t j = o.l / 21u;
-    const int sh = 61 - 3 * (int)(o.l - 21u * j);
-    o.c = o.l < lm ? (uint32_t)(s_words[j * GT_S + mem] >> sh) & 7u : 0u;
-    o.r = o.l < lr ? (uint32_t)(s_words[j * GT_S + ref] >> sh) & 7u : 0u;
+    o.c = o.l < lm ? sym_code(T3, pm + o.l) : 0u;
+    o.r = o.l < lr ? sym_code(T3, pr + o.l) : 0u;
     return o;
 }
 
@@ -269,8 +272,8 @@ __device__ __forceinline__ uint32_t class_l(uint32_t cls)
 
 // groups of at most 32 * R rows: one row per (slot, lane), keys in registers, shuffles only
 template <int R>
-__device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int W, const uint64_t *s_words,
-                                                 const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
+__device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
+                                                 const uint32_t *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
                                                  uint8_t *s_lcpout)
 {
     constexpr uint32_t IB = 6, IM = 63u;                  // position index bits
@@ -299,7 +302,7 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
                 const uint32_t idx = key[s] & IM;
                 if (rdepth[s] == 0xFFu) key[s] = (t << (13 + IB)) | idx;
                 else {
-                    const RefCmp o = ref_compare(s_words, s_len, W, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
+                    const RefCmp o = ref_compare(T3, s_pos, s_len, depth, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
                     key[s] = (runa[s] << (13 + IB)) | (class_of(o) << IB) | idx;
                 }
             }
@@ -386,8 +389,8 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
 }
 
 // groups of any size that fits the window: keys in shared memory, lanes stride over the rows
-__device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int lane, int W, const uint64_t *s_words,
-                                                 const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
+__device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
+                                                 const uint32_t *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
                                                  uint8_t *s_lcpout, uint64_t *s_key, uint16_t *s_runa, uint8_t *s_rdepth)
 {
     uint32_t n2 = 2;
@@ -412,7 +415,7 @@ __device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int 
             if (D == 0xFF) key[t] = ((uint64_t)t << 24) | idx;
             else {
                 const uint32_t a = s_runa[row];
-                const RefCmp o = ref_compare(s_words, s_len, W, gs + idx, s_best[a] & 0xFFFFu, D);
+                const RefCmp o = ref_compare(T3, s_pos, s_len, depth, gs + idx, s_best[a] & 0xFFFFu, D);
                 key[t] = ((uint64_t)(a - gs) << 24) | ((uint64_t)class_of(o) << 11) | idx;
             }
         }
@@ -478,9 +481,9 @@ __global__ void __launch_bounds__(GT_THREADS)
 group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
-    uint64_t *s_words = reinterpret_cast<uint64_t *>(gt_smem);                      // [W][GT_S] staged suffix words
-    uint64_t *s_key = s_words + (size_t)A.W * GT_S;                                 // [GT_S] keys of groups > 64 rows
-    uint32_t *s_best = reinterpret_cast<uint32_t *>(s_key + GT_S);                  // [GT_S] (length << 16 | row) of a run's reference
+    uint64_t *s_key = reinterpret_cast<uint64_t *>(gt_smem);                        // [GT_S] keys of groups > 64 rows
+    uint32_t *s_pos = reinterpret_cast<uint32_t *>(s_key + GT_S);                   // [GT_S] text position of the row's suffix
+    uint32_t *s_best = s_pos + GT_S;                                                // [GT_S] (length << 16 | row) of a run's reference
     uint32_t *s_head = s_best + GT_S;                                               // [GT_HW]
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] previous symbol code | its quality << 8
     uint16_t *s_gs = s_prev + GT_S;                                                 // [GT_S] group start or 0xFFFF (row not owned)
@@ -496,7 +499,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t t0 = blockIdx.x * (uint32_t)GT_T;
     const uint32_t m = A.m;
-    const int W = A.W, ksym = A.ksym;
+    const int ksym = A.ksym;
     const int depth = A.depth0 + ksym;
     const int kshift = 3 * ksym;                          // group id sits above the symbols (level >= 1)
     if (tid == 0) { s_ngroups = 0; s_next = 0; }
@@ -574,19 +577,8 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                         const uint32_t c = p > 0 ? sym_code(A.T3, (uint64_t)p - 1) : 0u;
                         s_prev[r] = (uint16_t)(c | ((c ? (ql & 255u) : (uint32_t)A.eos) << 8));
                     }
-                    if (size > 1) {
-                        const int slen = (int)(ql >> 8) - depth;          // symbols of this suffix past the shared prefix
-                        s_len[r] = (uint8_t)slen;
-                        for (int w = 0; w < W; w++) {
-                            const int v = slen - 21 * w;                     // valid symbols in this word
-                            uint64_t x = 0;
-                            if (v > 0) {
-                                x = text_window(A.T3, (uint64_t)p + depth + 21 * w);
-                                if (v < 21) x &= ~0ull << (64 - 3 * v);
-                            }
-                            s_words[w * GT_S + r] = x;
-                        }
-                    }
+                    s_pos[r] = p;
+                    s_len[r] = (uint8_t)max(0, (int)(ql >> 8) - depth);   // symbols of this suffix past the shared prefix
                 }
             }
         }
@@ -602,9 +594,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
         const uint32_t gs = s_gstart[g], len = s_glen[g];
-        if (len <= 32) order_group_regs<1>(gs, len, lane, W, s_words, s_len, s_best, s_sorted, s_lcpout);
-        else if (len <= 64) order_group_regs<2>(gs, len, lane, W, s_words, s_len, s_best, s_sorted, s_lcpout);
-        else order_group_smem(gs, len, lane, W, s_words, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
+        if (len <= 32) order_group_regs<1>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
+        else if (len <= 64) order_group_regs<2>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
+        else order_group_smem(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
         __syncwarp();
     }
     __syncthreads();
@@ -616,7 +608,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         const uint32_t j = t0 + r;
         const uint32_t e = s_sorted[r];
         const uint32_t slot = slot_of(j);
-        if (A.SA) A.SA[slot] = A.pos[t0 + e];
+        if (A.SA) A.SA[slot] = s_pos[e];
         if (A.bwt) {
             const uint32_t pv = s_prev[e];
             const uint32_t c = pv & 7u;
@@ -627,10 +619,10 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     }
 }
 
-static size_t group_tile_smem(int W)
+static size_t group_tile_smem(int)
 {
-    return (size_t)W * GT_S * 8 + (size_t)GT_S * 8 + (size_t)GT_S * 4 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 +
-           (size_t)GT_GMAX * 2 * 2 + (size_t)GT_S * 3 + 16;
+    return (size_t)GT_S * 8 + (size_t)GT_S * 4 * 2 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
+           (size_t)GT_S * 3 + 16;
 }
 
 // ============================================================================ deferred groups
@@ -744,7 +736,7 @@ static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgs &A)
 {
     const size_t smem = group_tile_smem(A.W);
     BFQ_CUDA(cudaFuncSetAttribute(group_tile_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ProfScope ps(c, PC_GROUP, (uint64_t)A.m * (sizeof(K) + 4 + 3 + 8 * (uint64_t)A.W));
+    ProfScope ps(c, PC_GROUP, (uint64_t)A.m * (sizeof(K) + 4 + 3 + 4 * (uint64_t)A.W));
     group_tile_kernel<K><<<div_up(A.m, GT_T), GT_THREADS, smem, c->stream>>>(keys, A);
     BFQ_CUDA(cudaGetLastError());
 }
