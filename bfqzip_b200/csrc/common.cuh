@@ -67,6 +67,32 @@ struct Arena {
     size_t total() const { size_t t = 0; for (auto &s : slabs) t += s.size; return t; }
 };
 
+// ---- packed text (3-bit codes, 64 symbols per three u64 words, first symbol in the most significant bits)
+#ifdef __CUDACC__
+// 21 symbols starting at text position p, in bits 63..1 (bit 0 cleared)
+__device__ __forceinline__ uint64_t text_window(const uint64_t *__restrict__ T3, uint64_t p)
+{
+    const uint64_t bit = 3 * p;
+    const uint64_t wi = bit >> 6;
+    const int s = (int)(bit & 63);
+    const uint64_t w0 = T3[wi], w1 = T3[wi + 1];
+    uint64_t r = s ? ((w0 << s) | (w1 >> (64 - s))) : w0;
+    return r & ~1ull;
+}
+
+// number of leading non-terminator symbols in a window (0..21)
+__device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
+{
+    const uint64_t M4 = 0x9249249249249248ull;   // top bit of each of the 21 fields (bits 63,60,...,3)
+    const uint64_t M3 = 0x6DB6DB6DB6DB6DB6ull;   // low two bits of each field
+    uint64_t t = ((w & M3) + M3) | w;            // field top bit set <=> field != 0
+    uint64_t zeros = ~t & M4;
+    int lz = zeros ? __clzll((long long)zeros) : 63;
+    return lz / 3;
+}
+
+#endif
+
 } // namespace bfq
 
 struct bfq_ctx {
@@ -151,6 +177,11 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P,
                  const uint64_t *d_off_known, uint8_t *d_out_bases, uint8_t *d_out_quals,
                  uint64_t *d_out_off, uint64_t *total_out);
 // radix.cu
+// Level-0 keys of the suffix sort: k symbols of every text position (cut at the terminator, QL[p] in the
+// unsorted bits 63..48 when given) with payload = position, built and histogrammed in one kernel, then sorted
+// on the 3k symbol bits.  Same result convention as radix_sort_pairs64.
+int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, uint64_t *keys_a,
+                           uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b);
 // Stable LSD sort of (key,val) on key bits [0,bits).  Result ends in keys_a/vals_a when the
 // returned flag is 0, in keys_b/vals_b when 1 (ping-pong buffers, both n long).
 int radix_sort_pairs64(bfq_ctx *c, uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a,

@@ -78,6 +78,35 @@ rs_hist_kernel(const K *__restrict__ keys, uint64_t n, RsPasses P, uint32_t *__r
     }
 }
 
+// level-0 suffix keys + their digit histograms in one pass over the packed text (see common.cuh)
+__global__ void __launch_bounds__(RS_THREADS)
+rs_suffix_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k, RsPasses P,
+                      uint64_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[2][RS_MAX_PASSES][RS_RADIX];
+    for (int i = threadIdx.x; i < 2 * RS_MAX_PASSES * RS_RADIX; i += RS_THREADS) (&sh[0][0][0])[i] = 0;
+    __syncthreads();
+    const int copy = (threadIdx.x >> 5) & 1;
+    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+    for (uint64_t p = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; p < n; p += stride) {
+        uint64_t w = text_window(T3, p);
+        const int f = leading_nonzero_fields(w);          // symbols before the first terminator
+        if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
+        uint64_t key = w >> (64 - 3 * k);
+#pragma unroll
+        for (int q = 0; q < RS_MAX_PASSES; q++)
+            if (q < P.num) atomicAdd(&sh[copy][q][digit_of(key, P.shift[q], (1u << P.bits[q]) - 1)], 1u);
+        if (QL) key |= (uint64_t)QL[p] << 48;             // rides in bits the sort ignores (k <= 16)
+        keys[p] = key;
+        vals[p] = (uint32_t)p;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < P.num * RS_RADIX; i += RS_THREADS) {
+        const uint32_t v = (&sh[0][0][0])[i] + (&sh[1][0][0])[i];
+        if (v) atomicAdd(&hist[i], v);
+    }
+}
+
 // exclusive scan of each pass's 256 counters, in place (one block per pass)
 __global__ void rs_scan_hist_kernel(uint32_t *hist)
 {
@@ -152,7 +181,12 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t d = digit_of(key[i], shift, mask);
-        uint32_t m = __match_any_sync(0xffffffffu, d);
+        // lanes with the same digit: one ballot per digit bit (match.any is far slower with ~30 distinct values per warp)
+        uint32_t m = 0xffffffffu;
+        for (int b = 0; b < bits; b++) {
+            const uint32_t vote = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+            m &= ((d >> b) & 1u) ? vote : ~vote;
+        }
         uint32_t prev = warp_cnt[w][d];
         __syncwarp();
         if ((__ffs(m) - 1) == lane) warp_cnt[w][d] = prev + __popc(m);
@@ -250,27 +284,19 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 }
 
 // ------------------------------------------------------------------------------ host driver
+// the passes, given the (unscanned) digit histograms of all of them
 template <typename K, int ITEMS>
-static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint32_t *vals_b,
-                            uint64_t n, int bits)
+static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint32_t *vals_b, uint64_t n,
+                        const RsPasses &P, uint32_t *hist)
 {
-    if (n == 0 || bits <= 0) return 0;
-    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
     constexpr int TILE = RS_THREADS * ITEMS;
-    RsPasses P = plan_passes(bits);
-    Arena::Mark mk = c->arena.mark();
     const uint32_t tiles = div_up(n, TILE);
     const bool wide = n >= ((uint64_t)1 << 30);
     const size_t status_bytes = (size_t)tiles * RS_RADIX * (wide ? 8 : 4) + 256;
-    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
     char *status = (char *)c->arena.alloc(status_bytes);
     uint32_t *tile_counter = (uint32_t *)(status + (size_t)tiles * RS_RADIX * (wide ? 8 : 4));
-
-    BFQ_CUDA(cudaMemsetAsync(hist, 0, RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), c->stream));
     {
-        ProfScope ps(c, PC_RADIX_HIST, n * sizeof(K), 2);
-        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
-        rs_hist_kernel<K><<<grid, RS_THREADS, 0, c->stream>>>(keys_a, n, P, hist);
+        ProfScope ps(c, PC_RADIX_HIST, 0, 1);
         rs_scan_hist_kernel<<<P.num, RS_RADIX, 0, c->stream>>>(hist);
     }
     K *kin = keys_a, *kout = keys_b;
@@ -292,10 +318,49 @@ static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, 
         std::swap(kin, kout);
         std::swap(vin, vout);
     }
+    return (P.num & 1);
+}
+
+template <typename K, int ITEMS>
+static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint32_t *vals_b,
+                            uint64_t n, int bits)
+{
+    if (n == 0 || bits <= 0) return 0;
+    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    RsPasses P = plan_passes(bits);
+    Arena::Mark mk = c->arena.mark();
+    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
+    BFQ_CUDA(cudaMemsetAsync(hist, 0, RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), c->stream));
+    {
+        ProfScope ps(c, PC_RADIX_HIST, n * sizeof(K), 1);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
+        rs_hist_kernel<K><<<grid, RS_THREADS, 0, c->stream>>>(keys_a, n, P, hist);
+    }
+    const int flip = radix_passes<K, ITEMS>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
     // The arena memory (hist/status) is reused by later allocations only after stream order
     // guarantees completion: everything runs on c->stream.
     c->arena.release(mk);
-    return (P.num & 1);
+    return flip;
+}
+
+int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, uint64_t *keys_a,
+                           uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b)
+{
+    if (n == 0) return 0;
+    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    RsPasses P = plan_passes(3 * k);
+    Arena::Mark mk = c->arena.mark();
+    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
+    BFQ_CUDA(cudaMemsetAsync(hist, 0, RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), c->stream));
+    {
+        ProfScope ps(c, PC_KEYS, n * (8 + 4 + 2) + n * 3 / 8);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
+        rs_suffix_keys_kernel<<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    const int flip = radix_passes<uint64_t, 16>(c, keys_a, keys_b, pos_a, pos_b, n, P, hist);
+    c->arena.release(mk);
+    return flip;
 }
 
 int radix_sort_pairs64(bfq_ctx *c, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, uint64_t n, int bits)

@@ -108,50 +108,9 @@ pack3_kernel(const uint8_t *__restrict__ T8, uint64_t n, uint64_t ngroups, uint6
     T3[g * 3 + 2] = w[2];
 }
 
-// 21 symbols starting at text position p, in bits 63..1 (bit 0 cleared)
-__device__ __forceinline__ uint64_t text_window(const uint64_t *__restrict__ T3, uint64_t p)
-{
-    const uint64_t bit = 3 * p;
-    const uint64_t wi = bit >> 6;
-    const int s = (int)(bit & 63);
-    const uint64_t w0 = T3[wi], w1 = T3[wi + 1];
-    uint64_t r = s ? ((w0 << s) | (w1 >> (64 - s))) : w0;
-    return r & ~1ull;
-}
-
-// number of leading non-terminator symbols in a window (0..21)
-__device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
-{
-    const uint64_t M4 = 0x9249249249249248ull;   // top bit of each of the 21 fields (bits 63,60,...,3)
-    const uint64_t M3 = 0x6DB6DB6DB6DB6DB6ull;   // low two bits of each field
-    uint64_t t = ((w & M3) + M3) | w;            // field top bit set <=> field != 0
-    uint64_t zeros = ~t & M4;
-    int lz = zeros ? __clzll((long long)zeros) : 63;
-    return lz / 3;
-}
-
 __device__ __forceinline__ uint32_t sym_code(const uint64_t *__restrict__ T3, uint64_t p)
 {
     return (uint32_t)(text_window(T3, p) >> 61);
-}
-
-// ============================================================================ initial keys
-template <typename K>
-__global__ void __launch_bounds__(256)
-init_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k,
-                 K *__restrict__ keys, uint32_t *__restrict__ vals)
-{
-    const uint32_t p = blockIdx.x * 256u + threadIdx.x;
-    if (p >= n) return;
-    uint64_t w = text_window(T3, p);
-    int f = leading_nonzero_fields(w);          // symbols before the first terminator
-    if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
-    // bits above the k symbols are not sorted on: QL[p] rides along there (k <= 16), so the group
-    // kernel gets the previous quality and the suffix length with the sequentially read key
-    uint64_t key = w >> (64 - 3 * k);
-    if (QL) key |= (uint64_t)QL[p] << 48;
-    keys[p] = (K)key;
-    vals[p] = p;
 }
 
 // ============================================================================ group tile kernel
@@ -790,11 +749,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     int k = c->opt_initial_k;
     if (k <= 0) k = 16;
     k = std::min(k, 21);
-    {
-        ProfScope ps(c, PC_KEYS, N * (8 + 4) + ngroups * 24);
-        init_keys_kernel<uint64_t><<<div_up(N, 256), 256, 0, st>>>(T3, k <= 16 ? QL : nullptr, (uint32_t)N, k, keyA, posA);
-    }
-    int flip = radix_sort_pairs64(c, keyA, keyB, posA, posB, N, 3 * k);
+    int flip = radix_sort_suffix_keys(c, T3, k <= 16 ? QL : nullptr, N, k, keyA, keyB, posA, posB);
     uint64_t *keys = flip ? keyB : keyA, *keys_alt = flip ? keyA : keyB;
     uint32_t *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
 
