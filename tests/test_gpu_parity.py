@@ -103,6 +103,16 @@ def test_part_a_huge_groups():
     assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
 
 
+def test_part_a_refuses_reads_longer_than_255():
+    """LCP entries are one byte and dataTypelenSeq is uchar (parameters.h:68): longer reads are an error, not a wrap."""
+    bases = np.frombuffer(b"ACGT" * 80, dtype=np.uint8)
+    quals = np.full(bases.size, 70, np.uint8)
+    off = np.array([0, 300, 320], np.uint64)
+    with pytest.raises(lib.BfqError) as ei:
+        ctx().build_ebwt(bases, quals, off, 35)
+    assert ei.value.code == -3
+
+
 @pytest.mark.parametrize("eos", [0, 35])
 def test_part_a_eos_byte(eos):
     """eGap writes 0, gsufsort '#': identical files otherwise."""
