@@ -62,10 +62,17 @@ static void check_reads_dev(bfq_ctx *c, const uint64_t *d_off, uint64_t nreads, 
 
 __global__ void __launch_bounds__(256)
 export_rows_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase, uint64_t n,
-                   uint64_t code2byte, uint8_t *__restrict__ qs_out, uint8_t *__restrict__ ob_out)
+                   uint64_t code2byte, uint8_t *__restrict__ qs_out, uint8_t *__restrict__ ob_out,
+                   const uint8_t *__restrict__ flat_bwt)
 {
     const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
     if (i >= n) return;
+    if (flat_bwt) {                                   // flat mode: lines is the per-row stored quality
+        const uint8_t q = lines[i];
+        qs_out[i] = q & 0x7F;
+        ob_out[i] = (q & 0x80) ? obase[i] : flat_bwt[i];
+        return;
+    }
     const uint8_t *L = lines + (i >> 5) * 64;
     const uint32_t *H = reinterpret_cast<const uint32_t *>(L);
     const uint32_t r = (uint32_t)(i & 31);
@@ -75,8 +82,9 @@ export_rows_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict_
     ob_out[i] = (q & 0x80) ? obase[i] : (uint8_t)(code2byte >> (8 * c));
 }
 
-static void remember(bfq_ctx *c, const SmoothResult &S)
+static void remember(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt = nullptr)
 {
+    c->last_flat_bwt = S.flat ? d_bwt : nullptr;
     c->last_lines = S.lines; c->last_obase = S.obase; c->last_n = S.n;
     memcpy(c->last_code2byte, S.alpha.code2byte, 8);
     c->has_last = true;
@@ -96,9 +104,14 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     if (!d_bwt) d_bwt = arena_alloc<uint8_t>(c, N + 64);
     if (!d_qs) d_qs = arena_alloc<uint8_t>(c, N + 64);
     if (!d_lcp) d_lcp = arena_alloc<uint8_t>(c, N + 64);
+    // Flat mode (no walk lines, no LF walk): the group kernel also writes the suffix array and the packed text is
+    // kept, so part B reads neighbours from the text and part C is a streaming sort back into text order.
+    const bool flat = mx <= (uint64_t)P->max_len && (c->opt_rebuild == 1 || (c->opt_rebuild == 0 && N >= (uint64_t)c->opt_flat_min_rows));
+    uint32_t *d_sa = flat ? arena_alloc<uint32_t>(c, N + 16) : nullptr;
+    uint64_t *d_t3 = flat ? arena_alloc<uint64_t>(c, packed_text_words(N)) : nullptr;
     {
         Arena::Mark mk = c->arena.mark();
-        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, P->eos_byte, d_bwt, d_qs, d_lcp, nullptr);
+        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, P->eos_byte, d_bwt, d_qs, d_lcp, d_sa, d_t3);
         c->arena.release(mk);        // sort scratch is dead (stream-ordered) once the gather is queued
     }
     if (h_bwt || h_qs || h_lcp) {
@@ -111,9 +124,11 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
         BFQ_CUDA(cudaEventRecord(c->ev_copy, c->copy_stream));
     }
     SmoothResult S;
-    smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats);
+    smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats, d_sa, d_t3);
     if (S.nreads != nreads) BFQ_FAIL(BFQ_ECUDA, "internal error: %llu end-markers for %llu reads", (unsigned long long)S.nreads, (unsigned long long)nreads);
-    if (mx <= (uint64_t)P->max_len) {
+    if (flat) {
+        unpermute_dev(c, S, d_bwt, d_sa, d_off, nreads, d_out_bases, d_out_quals);
+    } else if (mx <= (uint64_t)P->max_len) {
         rebuild_dev(c, S, P, d_off, d_out_bases, d_out_quals, nullptr, nullptr);
     } else {
         // reads longer than -l are truncated by the reference (decode.cpp:605): general path
@@ -122,7 +137,7 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     }
     if (h_bwt || h_qs || h_lcp) BFQ_CUDA(cudaStreamWaitEvent(c->stream, c->ev_copy, 0));   // side copies join the main stream
     BFQ_CUDA(cudaStreamSynchronize(c->stream));
-    remember(c, S);
+    remember(c, S, d_bwt);
 }
 
 } // namespace bfq
@@ -242,7 +257,7 @@ int bfq_export_rows(bfq_ctx *ctx, uint8_t *qs_out, uint8_t *obwt_out)
         uint8_t *dq = arena_alloc<uint8_t>(ctx, n + 64), *db = arena_alloc<uint8_t>(ctx, n + 64);
         uint64_t c2b = 0;
         for (int k = 0; k < 8; k++) c2b |= (uint64_t)ctx->last_code2byte[k] << (8 * k);
-        export_rows_kernel<<<div_up(n, 256), 256, 0, ctx->stream>>>(ctx->last_lines, ctx->last_obase, n, c2b, dq, db);
+        export_rows_kernel<<<div_up(n, 256), 256, 0, ctx->stream>>>(ctx->last_lines, ctx->last_obase, n, c2b, dq, db, ctx->last_flat_bwt);
         ctx->launches++;
         BFQ_CUDA(cudaMemcpyAsync(qs_out, dq, n, cudaMemcpyDeviceToHost, ctx->stream));
         BFQ_CUDA(cudaMemcpyAsync(obwt_out, db, n, cudaMemcpyDeviceToHost, ctx->stream));

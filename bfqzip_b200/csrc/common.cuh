@@ -91,6 +91,10 @@ __device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
     return lz / 3;
 }
 
+__device__ __forceinline__ uint32_t sym_code(const uint64_t *__restrict__ T3, uint64_t p)
+{
+    return (uint32_t)(text_window(T3, p) >> 61);
+}
 #endif
 
 } // namespace bfq
@@ -112,6 +116,8 @@ struct bfq_ctx {
     int opt_initial_k = 0;
     int64_t opt_long_cluster = 1024;
     int64_t opt_group_cap = 1 << 20;
+    int opt_rebuild = 0;                  // fused pipeline, part C: 0 auto, 1 streaming un-permute (flat), 2 inverse-LF walk
+    int64_t opt_flat_min_rows = 1 << 28;  // auto: flat mode from this many rows on
     int opt_profile = 0;
     // accounting
     uint64_t launches = 0;
@@ -120,6 +126,7 @@ struct bfq_ctx {
     // state kept after smooth/pipeline for bfq_export_rows
     const uint8_t *last_lines = nullptr;   // walk lines (device)
     const uint8_t *last_obase = nullptr;   // modified-base side array (device)
+    const uint8_t *last_flat_bwt = nullptr; // flat mode: the BWT bytes the stored qualities belong to
     uint64_t last_n = 0;
     uint8_t last_code2byte[8] = {0};
     bfq::Arena::Mark last_mark{0, 0};
@@ -161,22 +168,33 @@ struct EbwtDev {                 // device results of part A
 // sufsort.cu
 void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
                     uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos_byte,
-                    uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out);
+                    uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep = nullptr);
+size_t packed_text_words(uint64_t N);     // u64 words build_ebwt_dev needs for the packed text of N rows
 // smooth.cu
 struct SmoothResult {
     uint8_t *lines = nullptr;     // 64 B per 32 rows: u32 cnt[5], u32 plane[3], u8 q[32]
     uint8_t *obase = nullptr;     // n bytes, valid where q&0x80
+    bool flat = false;            // lines is a plain per-row array of stored qualities (no walk lines were built)
     uint64_t n = 0, nreads = 0;
     Alphabet alpha;
 };
+// d_sa / d_t3 (both or none): suffix array of the rows and the packed text from part A -> flat mode
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
-                uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats);
+                uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
+                const uint32_t *d_sa = nullptr, const uint64_t *d_t3 = nullptr);
 // rebuild.cu
 // d_len_known: per-read lengths offsets (nreads+1, u64) or NULL.  Writes reads in input order.
 void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P,
                  const uint64_t *d_off_known, uint8_t *d_out_bases, uint8_t *d_out_quals,
                  uint64_t *d_out_off, uint64_t *total_out);
+// Flat-mode rebuild: rows carry their text position (SA), so the smoothed (base, quality) of every row is put
+// back into text order by a streaming sort on SA - 1 instead of an inverse-LF walk.  off = read offsets.
+void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa,
+                   const uint64_t *d_off, uint64_t nreads, uint8_t *d_out_bases, uint8_t *d_out_quals);
 // radix.cu
+// Sorts (key, 16-bit payload) pairs whose keys are exactly the integers 0..n-1 in some order (applying a
+// permutation with streaming passes instead of a random scatter); the digit histograms are computed on the host.
+int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n);
 // Level-0 keys of the suffix sort: k symbols of every text position (cut at the terminator, QL[p] in the
 // unsorted bits 63..48 when given) with payload = position, built and histogrammed in one kernel, then sorted
 // on the 3k symbol bits.  Same result convention as radix_sort_pairs64.

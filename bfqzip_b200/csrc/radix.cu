@@ -138,10 +138,10 @@ template <typename S> __device__ __forceinline__ void st_status(S *p, S v)
     *((volatile S *)p) = v;
 }
 
-template <typename K, typename S, int ITEMS>
+template <typename K, typename V, typename S, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
-                   const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out,
+                   const V *__restrict__ vals_in, V *__restrict__ vals_out,
                    uint32_t n, int shift, int bits, const uint32_t *__restrict__ digit_base,
                    S *__restrict__ status, uint32_t *__restrict__ tile_counter)
 {
@@ -268,11 +268,11 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     __syncthreads();
 
     // ---- payload through the same permutation
-    uint32_t *stage32 = reinterpret_cast<uint32_t *>(stage);
+    V *stage32 = reinterpret_cast<V *>(stage);
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t loc = wbase + i * 32;
-        uint32_t v = (loc < valid) ? vals_in[tile_base + loc] : 0u;
+        V v = (loc < valid) ? vals_in[tile_base + loc] : (V)0;
         stage32[lpos[i]] = v;
     }
     __syncthreads();
@@ -285,8 +285,8 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 
 // ------------------------------------------------------------------------------ host driver
 // the passes, given the (unscanned) digit histograms of all of them
-template <typename K, int ITEMS>
-static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint32_t *vals_b, uint64_t n,
+template <typename K, typename V, int ITEMS>
+static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, uint64_t n,
                         const RsPasses &P, uint32_t *hist)
 {
     constexpr int TILE = RS_THREADS * ITEMS;
@@ -300,17 +300,17 @@ static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint
         rs_scan_hist_kernel<<<P.num, RS_RADIX, 0, c->stream>>>(hist);
     }
     K *kin = keys_a, *kout = keys_b;
-    uint32_t *vin = vals_a, *vout = vals_b;
+    V *vin = vals_a, *vout = vals_b;
     for (int p = 0; p < P.num; p++) {
         BFQ_CUDA(cudaMemsetAsync(status, 0, status_bytes, c->stream));
         {
-            ProfScope ps(c, PC_RADIX_PASS, 2 * n * (sizeof(K) + 4));
+            ProfScope ps(c, PC_RADIX_PASS, 2 * n * (sizeof(K) + sizeof(V)));
             if (wide)
-                rs_onesweep_kernel<K, uint64_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
+                rs_onesweep_kernel<K, V, uint64_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
                     kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
                     (uint64_t *)status, tile_counter);
             else
-                rs_onesweep_kernel<K, uint32_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
+                rs_onesweep_kernel<K, V, uint32_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
                     kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
                     (uint32_t *)status, tile_counter);
         }
@@ -336,7 +336,7 @@ static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, 
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
         rs_hist_kernel<K><<<grid, RS_THREADS, 0, c->stream>>>(keys_a, n, P, hist);
     }
-    const int flip = radix_passes<K, ITEMS>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
+    const int flip = radix_passes<K, uint32_t, ITEMS>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
     // The arena memory (hist/status) is reused by later allocations only after stream order
     // guarantees completion: everything runs on c->stream.
     c->arena.release(mk);
@@ -358,7 +358,37 @@ int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, u
         rs_suffix_keys_kernel<<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
         BFQ_CUDA(cudaGetLastError());
     }
-    const int flip = radix_passes<uint64_t, 16>(c, keys_a, keys_b, pos_a, pos_b, n, P, hist);
+    const int flip = radix_passes<uint64_t, uint32_t, 16>(c, keys_a, keys_b, pos_a, pos_b, n, P, hist);
+    c->arena.release(mk);
+    return flip;
+}
+
+// exact number of keys in [0, n) whose digit (shift, bits) equals d
+static uint32_t count_digit(uint64_t n, int shift, int bits, uint32_t d)
+{
+    const uint64_t period = (uint64_t)1 << (shift + bits), run = (uint64_t)1 << shift;
+    const uint64_t full = n / period, rem = n % period;
+    const uint64_t lo = (uint64_t)d << shift;
+    uint64_t c = full * run;
+    if (rem > lo) c += std::min(run, rem - lo);
+    return (uint32_t)c;
+}
+
+int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n)
+{
+    if (n == 0) return 0;
+    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    int bits = 1;
+    while (((uint64_t)1 << bits) < n) bits++;
+    RsPasses P = plan_passes(bits);
+    Arena::Mark mk = c->arena.mark();
+    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
+    std::vector<uint32_t> h(RS_MAX_PASSES * RS_RADIX, 0);
+    for (int p = 0; p < P.num; p++)
+        for (uint32_t d = 0; d < (1u << P.bits[p]); d++) h[p * RS_RADIX + d] = count_digit(n, P.shift[p], P.bits[p], d);
+    // pageable source: the copy is staged by the runtime before the call returns
+    BFQ_CUDA(cudaMemcpyAsync(hist, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    const int flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
     c->arena.release(mk);
     return flip;
 }

@@ -148,6 +148,65 @@ assemble_kernel(const uint8_t *__restrict__ sb, const uint8_t *__restrict__ sq, 
     }
 }
 
+// ---------------------------------------------------------------- flat mode: rebuild without the LF walk
+// Row i of the BWT holds the symbol at text position SA[i] - 1.  (text position, base | quality << 8) pairs are
+// sorted on the position -- the keys are exactly 0..n-1, so the passes are pure streaming (radix_sort_permutation)
+// -- and the reads are then copied out without their terminator slots.  At large n this replaces one dependent
+// 64-byte random fetch per base (DRAM sector / TLB bound) with ~64 streamed bytes per row.
+__global__ void __launch_bounds__(256)
+emit_pairs_kernel(const uint32_t *__restrict__ SA, const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qflat,
+                  const uint8_t *__restrict__ obase, uint32_t n, uint32_t *__restrict__ keys, uint16_t *__restrict__ vals)
+{
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p = SA[i];
+    const uint8_t q = qflat[i];
+    const uint8_t base = (q & 0x80) ? obase[i] : bwt[i];
+    keys[i] = p ? p - 1 : n - 1;                 // read starts land on a terminator slot (never copied out)
+    vals[i] = (uint16_t)(base | ((uint32_t)(q & 0x7F) << 8));
+}
+
+// one warp per read: text-order pairs (terminator slots included) -> the two output arrays
+__global__ void __launch_bounds__(256)
+compact_reads_kernel(const uint16_t *__restrict__ T, const uint64_t *__restrict__ off, uint64_t nreads,
+                     uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q)
+{
+    const int lane = threadIdx.x & 31;
+    const uint64_t warp0 = ((uint64_t)blockIdx.x * 256 + threadIdx.x) >> 5, nwarps = ((uint64_t)gridDim.x * 256) >> 5;
+    for (uint64_t d = warp0; d < nreads; d += nwarps) {
+        const uint64_t s = off[d], len = off[d + 1] - s, src = s + d;
+        for (uint64_t j = lane; j < len; j += 32) {
+            const uint16_t v = T[src + j];
+            out_b[s + j] = (uint8_t)v;
+            out_q[s + j] = (uint8_t)(v >> 8);
+        }
+    }
+}
+
+void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa,
+                   const uint64_t *d_off, uint64_t nreads, uint8_t *d_out_bases, uint8_t *d_out_quals)
+{
+    cudaStream_t st = c->stream;
+    const uint64_t n = S.n;
+    if (n == 0 || nreads == 0) return;
+    Arena::Mark mk = c->arena.mark();
+    uint32_t *ka = arena_alloc<uint32_t>(c, n + 16), *kb = arena_alloc<uint32_t>(c, n + 16);
+    uint16_t *va = arena_alloc<uint16_t>(c, n + 16), *vb = arena_alloc<uint16_t>(c, n + 16);
+    {
+        ProfScope ps(c, PC_WALK, n * (4 + 3 + 6));
+        emit_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, ka, va);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    const int flip = radix_sort_permutation(c, ka, kb, va, vb, n);
+    {
+        ProfScope ps(c, PC_ASSEMBLE, n * 2 + (n - nreads) * 2);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 16, div_up(nreads * 32, 256));
+        compact_reads_kernel<<<std::max(grid, 1), 256, 0, st>>>(flip ? vb : va, d_off, nreads, d_out_bases, d_out_quals);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    c->arena.release(mk);
+}
+
 void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P, const uint64_t *d_off_known,
                  uint8_t *d_out_bases, uint8_t *d_out_quals, uint64_t *d_out_off, uint64_t *total_out)
 {

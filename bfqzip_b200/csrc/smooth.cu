@@ -208,9 +208,11 @@ __device__ __forceinline__ uint32_t hdr_lf(const LineHdr &h, uint32_t r, uint32_
                   ((c & 4) ? h.plane[2] : ~h.plane[2]);
     return h.cnt[c - 1] + __popc(mm & ((1u << r) - 1u));
 }
-__device__ __forceinline__ uint8_t *line_q(uint8_t *lines, uint64_t row)
+// where the stored quality of a row lives: inside its walk line, or (FLAT, fused pipeline with the suffix
+// array at hand: no walk lines are built) in a plain per-row array
+template <bool FLAT> __device__ __forceinline__ uint8_t *q_slot(uint8_t *lines, uint64_t row)
 {
-    return lines + (row >> 5) * 64 + 32 + (row & 31);
+    return FLAT ? lines + row : lines + (row >> 5) * 64 + 32 + (row & 31);
 }
 
 // ------------------------------------------------------------------ cluster rules (shared)
@@ -348,6 +350,7 @@ __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stat
         atomicAdd(&g_stats[threadIdx.x], (unsigned long long)s_stats[threadIdx.x]);
 }
 
+template <bool FLAT>
 __global__ void __launch_bounds__(CL_THREADS)
 cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
@@ -450,7 +453,7 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
             if (d.act == ACT_RULE10) o = rule10_row(c, q, d.sym, acc.hiq, d.newqs, st);
             if (o & 0x80) obase[t0 + r] = symb;
             if (r < CL_TILE) { if (o != q) s_q[r] = o; }
-            else *line_q(lines, (uint64_t)(t0 + r)) = store_q(o);
+            else *q_slot<FLAT>(lines, (uint64_t)(t0 + r)) = store_q(o);
         }
     }
     __syncthreads();
@@ -458,12 +461,13 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     const uint32_t lead = s_lead;
     for (int r = tid; r < CL_TILE; r += CL_THREADS) {
         int64_t i = t0 + r;
-        if (i < nn && (uint32_t)r >= lead) *line_q(lines, (uint64_t)i) = store_q(s_q[r]);
+        if (i < nn && (uint32_t)r >= lead) *q_slot<FLAT>(lines, (uint64_t)i) = store_q(s_q[r]);
     }
     flush_stats(st, s_stats, L.stats);
 }
 
 // ------------------------------------------------------------------ long clusters: one block each
+template <bool FLAT>
 __global__ void __launch_bounds__(CL_THREADS)
 cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
@@ -567,7 +571,7 @@ cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
             uint8_t o = q;
             if (d.act == ACT_RULE10) o = rule10_row(c, q, d.sym, hiq, d.newqs, st);
             if (o & 0x80) obase[i] = symb;
-            *line_q(lines, (uint64_t)i) = store_q(o);
+            *q_slot<FLAT>(lines, (uint64_t)i) = store_q(o);
         }
         __syncthreads();
     }
@@ -577,14 +581,32 @@ cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
 // ------------------------------------------------------------------ rule 11: two frequent bases
 // bfq_ext.cpp:713-802 with buildLF_Cluster :415-476.  One warp per cluster; the symbol that
 // precedes row j in its read is bwt[LF(j)], two walk-line fetches.
+// FLAT: the row's symbol comes from the BWT bytes and the symbol before it in its read straight from the
+// packed text at SA[row] - 2 (code 0 there = the previous read's terminator = "no preceding base").
+template <bool FLAT>
 __global__ void __launch_bounds__(256)
 rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8_t *__restrict__ obase,
-              SmoothLists L)
+              SmoothLists L, const uint8_t *__restrict__ bwt, const uint32_t *__restrict__ SA,
+              const uint64_t *__restrict__ T3)
 {
     __shared__ uint32_t s_stats[ST_COUNT];
+    __shared__ uint8_t s_lut[256];
     const int tid = threadIdx.x, lane = tid & 31;
+    s_lut[tid] = g_sc.byte2code[tid];
     if (tid < ST_COUNT) s_stats[tid] = 0;
     __syncthreads();
+    auto row_code = [&](uint64_t i) -> uint32_t {
+        if (FLAT) return s_lut[bwt[i]];
+        LineHdr h = load_hdr(lines, i);
+        return hdr_code(h, (uint32_t)(i & 31));
+    };
+    auto prec_code = [&](uint64_t i, uint32_t c) -> uint32_t {      // symbol before row i's symbol c in its read
+        if (FLAT) { const uint32_t p = SA[i]; return p >= 2 ? sym_code(T3, (uint64_t)p - 2) : 0u; }
+        LineHdr h = load_hdr(lines, i);
+        const uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
+        LineHdr h2 = load_hdr(lines, r);
+        return hdr_code(h2, (uint32_t)(r & 31));
+    };
     uint32_t st[ST_COUNT];
 #pragma unroll
     for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
@@ -598,12 +620,9 @@ rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8
         uint32_t P0 = 0, P1 = 0;
         for (uint32_t j = lane; j < D.len; j += 32) {
             const uint64_t i = (uint64_t)D.start + j;
-            LineHdr h = load_hdr(lines, i);
-            uint32_t c = hdr_code(h, (uint32_t)(i & 31));
+            const uint32_t c = row_code(i);
             if (c == f0 || c == f1) {
-                uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
-                LineHdr h2 = load_hdr(lines, r);
-                uint32_t pc = hdr_code(h2, (uint32_t)(r & 31));
+                const uint32_t pc = prec_code(i, c);
                 if ((acgt >> pc) & 1u) { if (c == f0) P0 |= 1u << pc; else P1 |= 1u << pc; }
             }
         }
@@ -615,25 +634,22 @@ rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8
         const uint32_t prec0 = __ffs(P0) - 1, prec1 = __ffs(P1) - 1;
         for (uint32_t j = lane; j < D.len; j += 32) {
             const uint64_t i = (uint64_t)D.start + j;
-            LineHdr h = load_hdr(lines, i);
-            uint32_t c = hdr_code(h, (uint32_t)(i & 31));
+            const uint32_t c = row_code(i);
             if (c == 0) continue;
             const uint8_t q = qs[i];
             if (c != f0 && c != f1 && !((hiq >> c) & 1u)) {
-                uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
-                LineHdr h2 = load_hdr(lines, r);
-                uint32_t pc = hdr_code(h2, (uint32_t)(r & 31));
+                const uint32_t pc = prec_code(i, c);
                 uint32_t to = pc == prec0 ? f0 : (pc == prec1 ? f1 : 0u);
                 if (to) {
                     obase[i] = g_sc.code2byte[to];
-                    *line_q(lines, i) = store_q((uint8_t)(q | 0x80));
+                    *q_slot<FLAT>(lines, i) = store_q((uint8_t)(q | 0x80));
                     st[ST_MODIFIED]++;
                 }
             } else if (c == f0 || c == f1) {
-                *line_q(lines, i) = store_q(newqs);
+                *q_slot<FLAT>(lines, i) = store_q(newqs);
                 st[ST_SMOOTHED]++;
             } else if (newqs < q) {
-                *line_q(lines, i) = store_q(newqs);
+                *q_slot<FLAT>(lines, i) = store_q(newqs);
                 st[ST_SMOOTHED]++;
             }
         }
@@ -665,8 +681,11 @@ static void build_m1_tables(double errtab[256], double thr[128])
 static void launch_check(bfq_ctx *c) { BFQ_CUDA(cudaGetLastError()); (void)c; }
 
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
-                uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats)
+                uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
+                const uint32_t *d_sa, const uint64_t *d_t3)
 {
+    const bool flat = d_sa != nullptr && d_t3 != nullptr;
+    out->flat = flat;
     cudaStream_t st = c->stream;
     if (n >= ((uint64_t)1 << 32) - 64) BFQ_FAIL(BFQ_ETOOLARGE, "BWT has %llu rows; this build indexes rows with 32 bits", (unsigned long long)n);
     if (P->max_len <= 0 || P->max_len > 255) BFQ_FAIL(BFQ_EINVAL, "max_len must be 1..255 (dataTypelenSeq is uchar, parameters.h:68)");
@@ -713,12 +732,12 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
 
     // ---- walk lines (computeVectorUnbuildBCR, decode.cpp:87-235, + tableOcc)
     const uint64_t nlines = (n + 31) / 32;
-    out->lines = arena_alloc<uint8_t>(c, nlines * 64 + 64);
+    out->lines = flat ? arena_alloc<uint8_t>(c, n + 64) : arena_alloc<uint8_t>(c, nlines * 64 + 64);
     out->obase = arena_alloc<uint8_t>(c, n + 64);
     Arena::Mark mk = c->arena.mark();
-    const uint32_t nblk = div_up(n, RK_ROWS);
-    uint32_t *blk = arena_alloc<uint32_t>(c, (size_t)nblk * 8);
-    {
+    if (!flat) {
+        const uint32_t nblk = div_up(n, RK_ROWS);
+        uint32_t *blk = arena_alloc<uint32_t>(c, (size_t)nblk * 8);
         ProfScope ps(c, PC_RANK, 2 * n + nlines * 32, 3);
         rank_count_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, blk);
         rank_scan_kernel<<<1, 1024, 0, st>>>(blk, nblk, d_pile);
@@ -739,17 +758,20 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     BFQ_CUDA(cudaMemsetAsync(d_stats, 0, (ST_COUNT + 2) * 8, st));
     {
         ProfScope ps(c, PC_CLUSTER, 4 * n);
-        cluster_tile_kernel<<<div_up(n, CL_TILE), CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        if (flat) cluster_tile_kernel<true><<<div_up(n, CL_TILE), CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        else cluster_tile_kernel<false><<<div_up(n, CL_TILE), CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
         launch_check(c);
     }
     {
         ProfScope ps(c, PC_CLUSTER_LONG, 0);
-        cluster_long_kernel<<<c->num_sms * 2, CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        if (flat) cluster_long_kernel<true><<<c->num_sms * 2, CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        else cluster_long_kernel<false><<<c->num_sms * 2, CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
         launch_check(c);
     }
     {
         ProfScope ps(c, PC_RULE11, 0);
-        rule11_kernel<<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L);
+        if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, d_t3);
+        else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, d_t3);
         launch_check(c);
     }
     BFQ_CUDA(cudaMemcpyAsync(c->h_small, d_stats, (ST_COUNT + 2) * 8, cudaMemcpyDeviceToHost, st));

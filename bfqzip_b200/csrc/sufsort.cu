@@ -108,10 +108,6 @@ pack3_kernel(const uint8_t *__restrict__ T8, uint64_t n, uint64_t ngroups, uint6
     T3[g * 3 + 2] = w[2];
 }
 
-__device__ __forceinline__ uint32_t sym_code(const uint64_t *__restrict__ T3, uint64_t p)
-{
-    return (uint32_t)(text_window(T3, p) >> 61);
-}
 
 // ============================================================================ group tile kernel
 // After a stable radix sort on a key of `ksym` symbols (cut at the terminator) the list is a
@@ -700,9 +696,11 @@ static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgs &A)
     BFQ_CUDA(cudaGetLastError());
 }
 
+size_t packed_text_words(uint64_t N) { return ((N + 320 + 63) / 64) * 3 + 2; }
+
 void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
                     uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
-                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out)
+                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep)
 {
     const uint64_t N = total_bases + nreads;
     if (N == 0) return;
@@ -725,7 +723,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
 
     // ---- buffers
     const uint64_t ngroups = (N + 320 + 63) / 64;           // padded so windows past the end read zeros
-    uint64_t *T3 = arena_alloc<uint64_t>(c, ngroups * 3 + 2);
+    uint64_t *T3 = d_t3_keep ? d_t3_keep : arena_alloc<uint64_t>(c, ngroups * 3 + 2);
     uint16_t *QL = arena_alloc<uint16_t>(c, N + 16);
     uint64_t *keyA = arena_alloc<uint64_t>(c, N), *keyB = arena_alloc<uint64_t>(c, N);
     uint32_t *posA = arena_alloc<uint32_t>(c, N), *posB = arena_alloc<uint32_t>(c, N);

@@ -80,6 +80,8 @@ void bfq_ctx_destroy(bfq_ctx *ctx);
 /* Tunables (tests use them to force rarely-taken paths).  Unknown key -> BFQ_EINVAL.
  *   "initial_k"   symbols in the initial radix key (1..21, 0 = auto)
  *   "group_cap"   suffix groups with more members go to the next MSD level even when they fit a tile
+ *   "rebuild"     part C of the fused pipeline: 0 auto, 1 streaming un-permute through the suffix array, 2 inverse-LF walk
+ *   "flat_min_rows" auto mode switches to the un-permute from this many BWT rows on
  *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
  *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)      */
 int  bfq_ctx_set_option(bfq_ctx *ctx, const char *key, int64_t value);

@@ -200,16 +200,40 @@ def test_params_K_m(K, m):
 
 
 # ---------------------------------------------------------------- fused pipeline
+@pytest.mark.parametrize("rebuild", [1, 2], ids=["unpermute", "lfwalk"])
 @pytest.mark.parametrize("mode", MODES, ids=[f"M{m}B{b}" for m, b in MODES])
-def test_pipeline_vs_oracle(mode):
+def test_pipeline_vs_oracle(mode, rebuild):
+    """Both part-C paths of the fused pipeline: streaming un-permute through the suffix array (flat mode: no
+    walk lines, rule 11 reads the text) and the inverse-LF walk."""
     M, B = mode
     bases, quals, off = synth.make_reads(25000, 100, 500 + M * 2 + B)
-    (bwt, qs, lcp), (ob, oq), st = ctx(M, B).pipeline(bases, quals, off, lib.default_params(eos=0))
+    c = ctx(M, B)
+    c.set_option("rebuild", rebuild)
+    try:
+        (bwt, qs, lcp), (ob, oq), st = c.pipeline(bases, quals, off, lib.default_params(eos=0))
+        sq_g, ob_g = c.export_rows(len(bwt))
+    finally:
+        c.set_option("rebuild", 0)
     rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 0)
     assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
     eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B, eos=0))
     assert np.array_equal(ob, eb) and np.array_equal(oq, eq)
     assert all(st[k] == est[k] for k in STAT_KEYS)
+    assert len(sq_g) == len(bwt) and len(ob_g) == len(bwt)
+
+
+@pytest.mark.parametrize("rebuild", [1, 2], ids=["unpermute", "lfwalk"])
+def test_pipeline_variable_length_and_duplicates(rebuild):
+    g = np.load(os.path.join(H.GOLDEN, "syn_var_dup.npz"))
+    c = ctx(3, 1)
+    c.set_option("rebuild", rebuild)
+    try:
+        (bwt, qs, lcp), (ob, oq), st = c.pipeline(g["bases"], g["quals"], g["off"], lib.default_params(eos=35))
+    finally:
+        c.set_option("rebuild", 0)
+    assert np.array_equal(bwt, g["bwt"]) and np.array_equal(lcp, g["lcp"])
+    assert np.array_equal(ob, g["out_bases_M3_B1"]) and np.array_equal(oq, g["out_quals_M3_B1"])
+    assert [st[k] for k in STAT_KEYS] == [int(x) for x in g["stats_M3_B1"]]
 
 
 def test_pipeline_roundtrip_1M():
