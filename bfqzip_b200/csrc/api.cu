@@ -246,6 +246,59 @@ int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_qual
     API_END
 }
 
+int bfq_dist_build(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off, uint64_t nreads,
+                   uint64_t total_bases, const bfq_params *params, int rank, int world, uint64_t capacity,
+                   const uint64_t *text_bounds, uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_keys,
+                   uint16_t *d_vals, uint64_t *n_local, uint64_t *row_base, uint64_t *send_counts, bfq_stats *stats)
+{
+    API_BEGIN
+    if (!params || !d_off || !d_bases || !d_quals || !text_bounds || !d_bwt || !d_qs || !d_lcp || !d_keys || !d_vals || !n_local ||
+        !row_base || !send_counts)
+        BFQ_FAIL(BFQ_EINVAL, "bfq_dist_build: null pointer");
+    if (world < 1 || rank < 0 || rank >= world || world > 255) BFQ_FAIL(BFQ_EINVAL, "bfq_dist_build: rank %d of %d", rank, world);
+    // rows of different ranks never share a cluster only if a cluster needs more context than the range cut (4 symbols)
+    if (params->K < 4) BFQ_FAIL(BFQ_EINVAL, "single-collection mode over several GPUs needs -k >= 4 (ranges are cut on 4 symbols)");
+    bfq_ctx *c = ctx;
+    uint64_t mn, mx;
+    check_reads_dev(c, d_off, nreads, total_bases, &mn, &mx);
+    if (mx > (uint64_t)params->max_len) BFQ_FAIL(BFQ_EINVAL, "a read has %llu symbols, -l is %d", (unsigned long long)mx, params->max_len);
+    const uint64_t N = total_bases + nreads;
+    if (stats) memset(stats, 0, sizeof *stats);
+    *n_local = 0; *row_base = 0;
+    for (int d = 0; d < world; d++) send_counts[d] = 0;
+    if (N == 0) return BFQ_OK;
+    KeyRange R;
+    R.rank = rank; R.world = world; R.capacity = capacity;
+    uint32_t *d_sa = arena_alloc<uint32_t>(c, capacity + 16);
+    uint64_t *d_t3 = arena_alloc<uint64_t>(c, packed_text_words(N));
+    {
+        Arena::Mark mk = c->arena.mark();
+        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, params->eos_byte, d_bwt, d_qs, d_lcp, d_sa, d_t3, &R);
+        c->arena.release(mk);
+    }
+    *n_local = R.n_local; *row_base = R.row_base;
+    if (R.n_local) {
+        uint64_t ah[256];
+        memcpy(ah, c->base_hist, sizeof ah);
+        ah[params->eos_byte] += nreads;
+        SmoothResult S;
+        smooth_dev(c, d_bwt, d_qs, d_lcp, R.n_local, params, &S, stats, d_sa, d_t3, ah);
+        emit_sorted_pairs_dev(c, S, d_bwt, d_sa, N, text_bounds, world, d_keys, d_vals, send_counts);
+    }
+    if (stats) { stats->n = N; stats->nreads = nreads; }
+    BFQ_CUDA(cudaStreamSynchronize(c->stream));
+    API_END
+}
+
+int bfq_dist_place(bfq_ctx *ctx, uint32_t *d_keys, uint16_t *d_vals, uint64_t count, uint64_t text_lo, const uint64_t *d_off,
+                   uint64_t read_lo, uint64_t read_hi, uint8_t *d_out_bases, uint8_t *d_out_quals)
+{
+    API_BEGIN
+    if (count && (!d_keys || !d_vals || !d_off || !d_out_bases || !d_out_quals)) BFQ_FAIL(BFQ_EINVAL, "bfq_dist_place: null pointer");
+    place_pairs_dev(ctx, d_keys, d_vals, count, text_lo, d_off, read_lo, read_hi, d_out_bases, d_out_quals);
+    API_END
+}
+
 int bfq_export_rows(bfq_ctx *ctx, uint8_t *qs_out, uint8_t *obwt_out)
 {
     try {

@@ -128,6 +128,7 @@ struct bfq_ctx {
     const uint8_t *last_obase = nullptr;   // modified-base side array (device)
     const uint8_t *last_flat_bwt = nullptr; // flat mode: the BWT bytes the stored qualities belong to
     uint64_t last_n = 0;
+    uint64_t base_hist[256] = {0};   // byte histogram of the reads of the last part-A call
     uint8_t last_code2byte[8] = {0};
     bfq::Arena::Mark last_mark{0, 0};
     bool has_last = false;
@@ -166,9 +167,16 @@ struct EbwtDev {                 // device results of part A
 };
 
 // sufsort.cu
+struct KeyRange {                // single-collection mode: this rank builds only its slice of the global eBWT
+    int rank = 0, world = 1;
+    uint64_t capacity = 0;        // rows the output arrays can take
+    uint64_t n_local = 0;         // out: rows of this rank
+    uint64_t row_base = 0;        // out: global index of its first row
+};
 void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
                     uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos_byte,
-                    uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep = nullptr);
+                    uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep = nullptr,
+                    KeyRange *range = nullptr);
 size_t packed_text_words(uint64_t N);     // u64 words build_ebwt_dev needs for the packed text of N rows
 // smooth.cu
 struct SmoothResult {
@@ -181,7 +189,9 @@ struct SmoothResult {
 // d_sa / d_t3 (both or none): suffix array of the rows and the packed text from part A -> flat mode
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
                 uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
-                const uint32_t *d_sa = nullptr, const uint64_t *d_t3 = nullptr);
+                const uint32_t *d_sa = nullptr, const uint64_t *d_t3 = nullptr, const uint64_t *alpha_hist = nullptr);
+// alpha_hist: byte histogram that fixes the alphabet (single-collection mode: the rows are a slice of the global eBWT
+// and may miss a symbol); NULL = histogram of d_bwt itself, as buildFreq does.
 // rebuild.cu
 // d_len_known: per-read lengths offsets (nreads+1, u64) or NULL.  Writes reads in input order.
 void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P,
@@ -191,7 +201,20 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P,
 // back into text order by a streaming sort on SA - 1 instead of an inverse-LF walk.  off = read offsets.
 void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa,
                    const uint64_t *d_off, uint64_t nreads, uint8_t *d_out_bases, uint8_t *d_out_quals);
+// Single-collection mode, sending side: (text position, base | quality << 8) of every local row, sorted by position;
+// send_counts[d] = pairs whose position lies in [text_bounds[d], text_bounds[d + 1]).  n_total = rows of the global eBWT.
+void emit_sorted_pairs_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa, uint64_t n_total,
+                           const uint64_t *text_bounds, int world, uint32_t *d_keys, uint16_t *d_vals, uint64_t *send_counts);
+// receiving side: the pairs of text positions [t_lo, t_lo + cnt) in any order -> reads [read_lo, read_hi) in input order
+void place_pairs_dev(bfq_ctx *c, uint32_t *d_keys, uint16_t *d_vals, uint64_t cnt, uint64_t t_lo, const uint64_t *d_off,
+                     uint64_t read_lo, uint64_t read_hi, uint8_t *d_out_bases, uint8_t *d_out_quals);
 // radix.cu
+// Single-collection mode: the same, restricted to the suffixes whose key falls in the range of `rank` (ranges cut on
+// the first four symbols from a histogram all ranks compute identically).  n_local = suffixes of this rank,
+// row_base = rows of the global eBWT before them, prev_key / has_prev = key of the row just before the range.
+int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, int rank, int world,
+                                 uint64_t *keys_a, uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b, uint64_t capacity,
+                                 uint64_t *n_local, uint64_t *row_base, uint64_t *prev_key, bool *has_prev);
 // Sorts (key, 16-bit payload) pairs whose keys are exactly the integers 0..n-1 in some order (applying a
 // permutation with streaming passes instead of a random scatter); the digit histograms are computed on the host.
 int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n);
@@ -206,5 +229,7 @@ int radix_sort_pairs64(bfq_ctx *c, uint64_t *keys_a, uint64_t *keys_b, uint32_t 
                        uint32_t *vals_b, uint64_t n, int bits);
 int radix_sort_pairs32(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a,
                        uint32_t *vals_b, uint64_t n, int bits);
+int radix_sort_pairs32_16(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a,
+                          uint16_t *vals_b, uint64_t n, int bits);
 
 } // namespace bfq

@@ -321,8 +321,8 @@ static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, 
     return (P.num & 1);
 }
 
-template <typename K, int ITEMS>
-static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, uint32_t *vals_b,
+template <typename K, int ITEMS, typename V = uint32_t>
+static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b,
                             uint64_t n, int bits)
 {
     if (n == 0 || bits <= 0) return 0;
@@ -336,9 +336,196 @@ static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, uint32_t *vals_a, 
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
         rs_hist_kernel<K><<<grid, RS_THREADS, 0, c->stream>>>(keys_a, n, P, hist);
     }
-    const int flip = radix_passes<K, uint32_t, ITEMS>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
+    const int flip = radix_passes<K, V, ITEMS>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
     // The arena memory (hist/status) is reused by later allocations only after stream order
     // guarantees completion: everything runs on c->stream.
+    c->arena.release(mk);
+    return flip;
+}
+
+// ------------------------------------------------------------------------------ key-range selection
+// Single-collection mode over several GPUs: every rank holds the whole packed text and sorts only the suffixes
+// whose key lies in its range.  The ranges are cut on the first four symbols (top 12 of the 48 key bits) from a
+// histogram every rank computes identically, so no splitter exchange is needed and equal keys never straddle ranks.
+__device__ __forceinline__ uint64_t suffix_key(const uint64_t *__restrict__ T3, uint64_t p, int k)
+{
+    uint64_t w = text_window(T3, p);
+    const int f = leading_nonzero_fields(w);          // symbols before the first terminator
+    if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
+    return w >> (64 - 3 * k);
+}
+
+constexpr int RS_TOP_BITS = 12;
+constexpr int RS_SEL_ITEMS = 16;                      // consecutive positions per thread in the selection kernels
+constexpr int RS_SEL_CHUNK = RS_THREADS * RS_SEL_ITEMS;
+
+__global__ void __launch_bounds__(RS_THREADS)
+rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint32_t n, int k, uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[1 << RS_TOP_BITS];
+    for (int i = threadIdx.x; i < (1 << RS_TOP_BITS); i += RS_THREADS) sh[i] = 0;
+    __syncthreads();
+    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+    for (uint64_t p = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; p < n; p += stride)
+        atomicAdd(&sh[(uint32_t)(suffix_key(T3, p, k) >> (3 * k - RS_TOP_BITS))], 1u);
+    __syncthreads();
+    for (int i = threadIdx.x; i < (1 << RS_TOP_BITS); i += RS_THREADS)
+        if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+// WRITE = false: per-chunk count of selected positions and the largest key below the range;
+// WRITE = true : ordered compaction (position order is kept: the sort relies on it for ties) + digit histograms
+template <bool WRITE>
+__global__ void __launch_bounds__(RS_THREADS)
+rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k, uint64_t lo,
+                 uint64_t hi, RsPasses P, uint32_t *__restrict__ chunk_count, const uint32_t *__restrict__ chunk_base,
+                 unsigned long long *__restrict__ prev_key, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals,
+                 uint32_t *__restrict__ hist)
+{
+    __shared__ uint32_t sh[WRITE ? RS_MAX_PASSES * RS_RADIX : 1];
+    __shared__ uint32_t s_warp[RS_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (WRITE) { for (int i = tid; i < RS_MAX_PASSES * RS_RADIX; i += RS_THREADS) sh[i] = 0; __syncthreads(); }
+    const uint64_t p0 = (uint64_t)blockIdx.x * RS_SEL_CHUNK + (uint64_t)tid * RS_SEL_ITEMS;
+    uint64_t key[RS_SEL_ITEMS];
+    uint32_t mine = 0;
+    unsigned long long below = 0; bool any_below = false;
+#pragma unroll
+    for (int i = 0; i < RS_SEL_ITEMS; i++) {
+        const uint64_t p = p0 + i;
+        key[i] = ~0ull;
+        if (p < n) {
+            const uint64_t kk = suffix_key(T3, p, k);
+            if (kk >= lo && kk < hi) { key[i] = kk; mine++; }
+            else if (!WRITE && kk < lo) { below = max(below, (unsigned long long)kk); any_below = true; }
+        }
+    }
+    uint32_t x = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) s_warp[w] = x;
+    __syncthreads();
+    uint32_t add = 0, total = 0;
+    for (int i = 0; i < RS_WARPS; i++) { if (i < w) add += s_warp[i]; total += s_warp[i]; }
+    if (!WRITE) {
+        if (tid == 0) chunk_count[blockIdx.x] = total;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            below = max(below, (unsigned long long)__shfl_xor_sync(0xffffffffu, below, o));
+            any_below |= (bool)__shfl_xor_sync(0xffffffffu, (int)any_below, o);
+        }
+        if (lane == 0 && any_below) atomicMax(prev_key, below | (1ull << 63));      // bit 63 = "a key below the range exists"
+        return;
+    }
+    uint32_t dst = chunk_base[blockIdx.x] + add + x - mine;
+#pragma unroll
+    for (int i = 0; i < RS_SEL_ITEMS; i++) {
+        if (key[i] != ~0ull) {
+            const uint64_t p = p0 + i;
+#pragma unroll
+            for (int q = 0; q < RS_MAX_PASSES; q++)
+                if (q < P.num) atomicAdd(&sh[q * RS_RADIX + digit_of(key[i], P.shift[q], (1u << P.bits[q]) - 1)], 1u);
+            keys[dst] = QL ? (key[i] | ((uint64_t)QL[p] << 48)) : key[i];
+            vals[dst] = (uint32_t)p;
+            dst++;
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < P.num * RS_RADIX; i += RS_THREADS)
+        if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+__global__ void __launch_bounds__(1024)
+rs_scan_chunks_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out, uint32_t n, uint32_t *__restrict__ total)
+{
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += 1024) {
+        const uint32_t i = base + tid;
+        const uint32_t v = i < n ? in[i] : 0u;
+        uint32_t x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) s_warp[w] = x;
+        __syncthreads();
+        uint32_t add = 0;
+        for (int j = 0; j < w; j++) add += s_warp[j];
+        const uint32_t carry = s_carry;
+        if (i < n) out[i] = carry + add + x - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + add + x;
+        __syncthreads();
+    }
+    if (tid == 0) *total = s_carry;
+}
+
+int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, int rank, int world,
+                                 uint64_t *keys_a, uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b, uint64_t capacity,
+                                 uint64_t *n_local, uint64_t *row_base, uint64_t *prev_key, bool *has_prev)
+{
+    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    if (3 * k < RS_TOP_BITS) BFQ_FAIL(BFQ_EINVAL, "the key-range split needs an initial key of at least 4 symbols");
+    cudaStream_t st = c->stream;
+    RsPasses P = plan_passes(3 * k);
+    Arena::Mark mk = c->arena.mark();
+    const uint32_t nchunks = div_up(n, RS_SEL_CHUNK);
+    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
+    uint32_t *top = arena_alloc<uint32_t>(c, 1 << RS_TOP_BITS);
+    uint32_t *cc = arena_alloc<uint32_t>(c, nchunks + 1), *cb = arena_alloc<uint32_t>(c, nchunks + 1);
+    unsigned long long *d_prev = arena_alloc<unsigned long long>(c, 2);
+    BFQ_CUDA(cudaMemsetAsync(hist, 0, RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), st));
+    BFQ_CUDA(cudaMemsetAsync(top, 0, sizeof(uint32_t) << RS_TOP_BITS, st));
+    BFQ_CUDA(cudaMemsetAsync(d_prev, 0, 16, st));
+    std::vector<uint32_t> h(1 << RS_TOP_BITS);
+    {
+        ProfScope ps(c, PC_KEYS, n * 3 / 8);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
+        rs_top_hist_kernel<<<grid, RS_THREADS, 0, st>>>(T3, (uint32_t)n, k, top);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    BFQ_CUDA(cudaMemcpyAsync(h.data(), top, h.size() * 4, cudaMemcpyDeviceToHost, st));
+    BFQ_CUDA(cudaStreamSynchronize(st));
+    // rank r takes the bins [b_r, b_{r+1}) with b_r = first bin whose cumulative count reaches r * n / world
+    auto bin_of = [&](int r) -> uint32_t {
+        if (r <= 0) return 0;
+        if (r >= world) return 1u << RS_TOP_BITS;
+        const uint64_t want = n / (uint64_t)world * (uint64_t)r;
+        uint64_t cum = 0;
+        for (uint32_t b = 0; b < (1u << RS_TOP_BITS); b++) { if (cum >= want) return b; cum += h[b]; }
+        return 1u << RS_TOP_BITS;
+    };
+    const uint32_t b0 = bin_of(rank), b1 = bin_of(rank + 1);
+    uint64_t below = 0;
+    for (uint32_t b = 0; b < b0; b++) below += h[b];
+    const int sh = 3 * k - RS_TOP_BITS;
+    const uint64_t lo = (uint64_t)b0 << sh, hi = (uint64_t)b1 << sh;
+    {
+        ProfScope ps(c, PC_KEYS, n * 3 / 8, 2);
+        rs_select_kernel<false><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, (uint32_t)n, k, lo, hi, P, cc, nullptr, d_prev, nullptr, nullptr, nullptr);
+        rs_scan_chunks_kernel<<<1, 1024, 0, st>>>(cc, cb, nchunks, (uint32_t *)(d_prev + 1));
+        BFQ_CUDA(cudaGetLastError());
+    }
+    BFQ_CUDA(cudaMemcpyAsync(c->h_small, d_prev, 16, cudaMemcpyDeviceToHost, st));
+    BFQ_CUDA(cudaStreamSynchronize(st));
+    const uint64_t pk = c->h_small[0];
+    const uint64_t cnt = (uint32_t)c->h_small[1];
+    *has_prev = (pk >> 63) != 0;
+    *prev_key = pk & ~(1ull << 63);
+    *n_local = cnt;
+    *row_base = below;
+    if (cnt > capacity) BFQ_FAIL(BFQ_ECAPACITY, "rank %d of %d sorts %llu suffixes, capacity is %llu", rank, world, (unsigned long long)cnt, (unsigned long long)capacity);
+    int flip = 0;
+    if (cnt) {
+        {
+            ProfScope ps(c, PC_KEYS, n * 3 / 8 + cnt * 14);
+            rs_select_kernel<true><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, (uint32_t)n, k, lo, hi, P, nullptr, cb, nullptr, keys_a, pos_a, hist);
+            BFQ_CUDA(cudaGetLastError());
+        }
+        flip = radix_passes<uint64_t, uint32_t, 16>(c, keys_a, keys_b, pos_a, pos_b, cnt, P, hist);
+    }
     c->arena.release(mk);
     return flip;
 }
@@ -400,6 +587,10 @@ int radix_sort_pairs64(bfq_ctx *c, uint64_t *ka, uint64_t *kb, uint32_t *va, uin
 int radix_sort_pairs32(bfq_ctx *c, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, uint64_t n, int bits)
 {
     return radix_sort_pairs<uint32_t, 16>(c, ka, kb, va, vb, n, bits);
+}
+int radix_sort_pairs32_16(bfq_ctx *c, uint32_t *ka, uint32_t *kb, uint16_t *va, uint16_t *vb, uint64_t n, int bits)
+{
+    return radix_sort_pairs<uint32_t, 16, uint16_t>(c, ka, kb, va, vb, n, bits);
 }
 
 } // namespace bfq

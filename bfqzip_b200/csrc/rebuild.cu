@@ -155,30 +155,33 @@ assemble_kernel(const uint8_t *__restrict__ sb, const uint8_t *__restrict__ sq, 
 // 64-byte random fetch per base (DRAM sector / TLB bound) with ~64 streamed bytes per row.
 __global__ void __launch_bounds__(256)
 emit_pairs_kernel(const uint32_t *__restrict__ SA, const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qflat,
-                  const uint8_t *__restrict__ obase, uint32_t n, uint32_t *__restrict__ keys, uint16_t *__restrict__ vals)
+                  const uint8_t *__restrict__ obase, uint32_t n, uint32_t *__restrict__ keys, uint16_t *__restrict__ vals,
+                  uint32_t n_total)
 {
     const uint32_t i = blockIdx.x * 256u + threadIdx.x;
     if (i >= n) return;
     const uint32_t p = SA[i];
     const uint8_t q = qflat[i];
     const uint8_t base = (q & 0x80) ? obase[i] : bwt[i];
-    keys[i] = p ? p - 1 : n - 1;                 // read starts land on a terminator slot (never copied out)
+    keys[i] = p ? p - 1 : n_total - 1;                 // read starts land on a terminator slot (never copied out)
     vals[i] = (uint16_t)(base | ((uint32_t)(q & 0x7F) << 8));
 }
 
 // one warp per read: text-order pairs (terminator slots included) -> the two output arrays
+// reads [read_lo, read_lo + nreads): T starts at text position t_lo, the outputs at base offset off[read_lo]
 __global__ void __launch_bounds__(256)
 compact_reads_kernel(const uint16_t *__restrict__ T, const uint64_t *__restrict__ off, uint64_t nreads,
-                     uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q)
+                     uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q, uint64_t read_lo = 0, uint64_t t_lo = 0)
 {
     const int lane = threadIdx.x & 31;
     const uint64_t warp0 = ((uint64_t)blockIdx.x * 256 + threadIdx.x) >> 5, nwarps = ((uint64_t)gridDim.x * 256) >> 5;
-    for (uint64_t d = warp0; d < nreads; d += nwarps) {
-        const uint64_t s = off[d], len = off[d + 1] - s, src = s + d;
+    const uint64_t o_lo = read_lo ? off[read_lo] : 0;
+    for (uint64_t d = read_lo + warp0; d < read_lo + nreads; d += nwarps) {
+        const uint64_t s = off[d], len = off[d + 1] - s, src = s + d - t_lo, dst = s - o_lo;
         for (uint64_t j = lane; j < len; j += 32) {
             const uint16_t v = T[src + j];
-            out_b[s + j] = (uint8_t)v;
-            out_q[s + j] = (uint8_t)(v >> 8);
+            out_b[dst + j] = (uint8_t)v;
+            out_q[dst + j] = (uint8_t)(v >> 8);
         }
     }
 }
@@ -194,7 +197,7 @@ void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, cons
     uint16_t *va = arena_alloc<uint16_t>(c, n + 16), *vb = arena_alloc<uint16_t>(c, n + 16);
     {
         ProfScope ps(c, PC_WALK, n * (4 + 3 + 6));
-        emit_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, ka, va);
+        emit_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, ka, va, (uint32_t)n);
         BFQ_CUDA(cudaGetLastError());
     }
     const int flip = radix_sort_permutation(c, ka, kb, va, vb, n);
@@ -204,6 +207,83 @@ void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, cons
         compact_reads_kernel<<<std::max(grid, 1), 256, 0, st>>>(flip ? vb : va, d_off, nreads, d_out_bases, d_out_quals);
         BFQ_CUDA(cudaGetLastError());
     }
+    c->arena.release(mk);
+}
+
+// ---------------------------------------------------------------- single-collection mode over several GPUs
+__global__ void bound_counts_kernel(const uint32_t *__restrict__ keys, uint32_t n, const uint64_t *__restrict__ bounds, int world,
+                                    unsigned long long *__restrict__ lower)
+{
+    const int d = threadIdx.x;
+    if (d > world) return;
+    const uint64_t b = bounds[d];
+    uint32_t lo = 0, hi = n;                      // first index with key >= b
+    while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if ((uint64_t)keys[mid] < b) lo = mid + 1; else hi = mid; }
+    lower[d] = lo;
+}
+
+__global__ void __launch_bounds__(256) rebase_keys_kernel(uint32_t *__restrict__ keys, uint64_t n, uint32_t base)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i < n) keys[i] -= base;
+}
+
+void emit_sorted_pairs_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa, uint64_t n_total,
+                           const uint64_t *text_bounds, int world, uint32_t *d_keys, uint16_t *d_vals, uint64_t *send_counts)
+{
+    cudaStream_t st = c->stream;
+    const uint64_t n = S.n;
+    for (int d = 0; d < world; d++) send_counts[d] = 0;
+    if (n == 0) return;
+    if (world + 1 > 256) BFQ_FAIL(BFQ_EINVAL, "at most 255 ranks");
+    Arena::Mark mk = c->arena.mark();
+    uint32_t *kb = arena_alloc<uint32_t>(c, n + 16);
+    uint16_t *vb = arena_alloc<uint16_t>(c, n + 16);
+    uint64_t *d_bounds = arena_alloc<uint64_t>(c, 2 * (world + 1));
+    unsigned long long *d_lower = (unsigned long long *)(d_bounds + world + 1);
+    {
+        ProfScope ps(c, PC_WALK, n * (4 + 3 + 6));
+        emit_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, d_keys, d_vals, (uint32_t)n_total);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    int bits = 1;
+    while (((uint64_t)1 << bits) < n_total) bits++;
+    const int flip = radix_sort_pairs32_16(c, d_keys, kb, d_vals, vb, n, bits);
+    if (flip) {
+        BFQ_CUDA(cudaMemcpyAsync(d_keys, kb, n * 4, cudaMemcpyDeviceToDevice, st));
+        BFQ_CUDA(cudaMemcpyAsync(d_vals, vb, n * 2, cudaMemcpyDeviceToDevice, st));
+    }
+    BFQ_CUDA(cudaMemcpyAsync(d_bounds, text_bounds, (world + 1) * 8, cudaMemcpyHostToDevice, st));
+    bound_counts_kernel<<<1, 256, 0, st>>>(d_keys, (uint32_t)n, d_bounds, world, d_lower);
+    BFQ_CUDA(cudaGetLastError());
+    std::vector<uint64_t> lower(world + 1);
+    BFQ_CUDA(cudaMemcpyAsync(lower.data(), d_lower, (world + 1) * 8, cudaMemcpyDeviceToHost, st));
+    BFQ_CUDA(cudaStreamSynchronize(st));
+    for (int d = 0; d < world; d++) send_counts[d] = lower[d + 1] - lower[d];
+    c->arena.release(mk);
+}
+
+void place_pairs_dev(bfq_ctx *c, uint32_t *d_keys, uint16_t *d_vals, uint64_t cnt, uint64_t t_lo, const uint64_t *d_off,
+                     uint64_t read_lo, uint64_t read_hi, uint8_t *d_out_bases, uint8_t *d_out_quals)
+{
+    cudaStream_t st = c->stream;
+    if (cnt == 0 || read_hi <= read_lo) return;
+    Arena::Mark mk = c->arena.mark();
+    uint32_t *kb = arena_alloc<uint32_t>(c, cnt + 16);
+    uint16_t *vb = arena_alloc<uint16_t>(c, cnt + 16);
+    if (t_lo) {
+        rebase_keys_kernel<<<div_up(cnt, 256), 256, 0, st>>>(d_keys, cnt, (uint32_t)t_lo);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    const int flip = radix_sort_permutation(c, d_keys, kb, d_vals, vb, cnt);
+    {
+        const uint64_t nreads = read_hi - read_lo;
+        ProfScope ps(c, PC_ASSEMBLE, cnt * 2 + (cnt - nreads) * 2);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 16, div_up(nreads * 32, 256));
+        compact_reads_kernel<<<std::max(grid, 1), 256, 0, st>>>(flip ? vb : d_vals, d_off, nreads, d_out_bases, d_out_quals, read_lo, t_lo);
+        BFQ_CUDA(cudaGetLastError());
+    }
+    BFQ_CUDA(cudaStreamSynchronize(st));
     c->arena.release(mk);
 }
 

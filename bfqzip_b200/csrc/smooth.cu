@@ -682,7 +682,7 @@ static void launch_check(bfq_ctx *c) { BFQ_CUDA(cudaGetLastError()); (void)c; }
 
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
                 uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
-                const uint32_t *d_sa, const uint64_t *d_t3)
+                const uint32_t *d_sa, const uint64_t *d_t3, const uint64_t *alpha_hist)
 {
     const bool flat = d_sa != nullptr && d_t3 != nullptr;
     out->flat = flat;
@@ -696,7 +696,7 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     byte_histogram(c, d_qs, n, qhist);
     for (int b = 128; b < 256; b++)
         if (qhist[b]) BFQ_FAIL(BFQ_EINVAL, "quality byte %d >= 128 is not a FASTQ quality", b);
-    Alphabet A = alphabet_from_hist(hist, P->eos_byte, /*eos_may_appear=*/true);
+    Alphabet A = alphabet_from_hist(alpha_hist ? alpha_hist : hist, P->eos_byte, /*eos_may_appear=*/true);
     out->alpha = A;
     out->n = n;
     out->nreads = hist[P->eos_byte];

@@ -151,6 +151,8 @@ struct GroupTileArgs {
     uint32_t *defer_count;      // [0] groups deferred, [1] members (filled by defer_len_kernel)
     uint32_t *defer_start;      // list index of the head of every deferred group
     uint32_t defer_cap;
+    uint64_t prev_key;          // level 0 of a key range: key of the global row just before this list (has_prev)
+    int has_prev;
     uint64_t kmask;             // key bits that take part in group equality (level 0: the 3*ksym symbol bits)
     int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
@@ -505,7 +507,10 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                     // head row: its LCP comes from the keys and is final at this level
                     if (A.lcp) {
                         bool write = true; uint32_t l = 0;
-                        if (j == 0) write = A.level0;
+                        if (j == 0) {
+                            write = A.level0;
+                            if (A.level0 && A.has_prev) l = head_lcp<K>((K)A.prev_key, keys[0] & (K)A.kmask, ksym);
+                        }
                         else {
                             const K kc = keys[j] & (K)A.kmask, kp = keys[j - 1] & (K)A.kmask;
                             if (!A.level0 && ((uint64_t)kc >> kshift) != ((uint64_t)kp >> kshift)) write = false;   // written one level up
@@ -700,7 +705,7 @@ size_t packed_text_words(uint64_t N) { return ((N + 320 + 63) / 64) * 3 + 2; }
 
 void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
                     uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
-                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep)
+                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep, KeyRange *range)
 {
     const uint64_t N = total_bases + nreads;
     if (N == 0) return;
@@ -713,6 +718,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     // ---- alphabet from the data (codes follow byte order, like gsufsort's +1 remap)
     uint64_t hist[256];
     byte_histogram(c, d_bases, total_bases, hist);
+    memcpy(c->base_hist, hist, sizeof hist);
     Alphabet A = alphabet_from_hist(hist, eos, /*eos_may_appear=*/false);
     // gsufsort drops bytes <= 1 and 255 (utils.c:229-236); refuse them instead of silently differing
     if (hist[0] || hist[1] || hist[255]) BFQ_FAIL(BFQ_EALPHABET, "bytes 0, 1 or 255 inside reads are not supported");
@@ -725,8 +731,10 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     const uint64_t ngroups = (N + 320 + 63) / 64;           // padded so windows past the end read zeros
     uint64_t *T3 = d_t3_keep ? d_t3_keep : arena_alloc<uint64_t>(c, ngroups * 3 + 2);
     uint16_t *QL = arena_alloc<uint16_t>(c, N + 16);
-    uint64_t *keyA = arena_alloc<uint64_t>(c, N), *keyB = arena_alloc<uint64_t>(c, N);
-    uint32_t *posA = arena_alloc<uint32_t>(c, N), *posB = arena_alloc<uint32_t>(c, N);
+    // a key range sorts about N / world suffixes; keyB also hosts the byte text (N + 1 bytes) while packing
+    const uint64_t cap = range ? std::max<uint64_t>(range->capacity, N / 8 + 64) : N;
+    uint64_t *keyA = arena_alloc<uint64_t>(c, cap), *keyB = arena_alloc<uint64_t>(c, cap);
+    uint32_t *posA = arena_alloc<uint32_t>(c, cap), *posB = arena_alloc<uint32_t>(c, cap);
     const uint32_t dcap = (uint32_t)(N / std::min<uint64_t>(GT_E, (uint64_t)c->opt_group_cap + 1) + 64);
     uint32_t *dtab[2][4];                                   // per level parity: start, len, slot, off
     for (int a = 0; a < 2; a++)
@@ -747,7 +755,16 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     int k = c->opt_initial_k;
     if (k <= 0) k = 16;
     k = std::min(k, 21);
-    int flip = radix_sort_suffix_keys(c, T3, k <= 16 ? QL : nullptr, N, k, keyA, keyB, posA, posB);
+    int flip;
+    uint64_t n_sort = N, prev_key = 0;
+    bool has_prev = false;
+    if (range) {
+        flip = radix_sort_suffix_keys_range(c, T3, k <= 16 ? QL : nullptr, N, k, range->rank, range->world, keyA, keyB, posA, posB,
+                                            range->capacity, &range->n_local, &range->row_base, &prev_key, &has_prev);
+        n_sort = range->n_local;
+        if (n_sort == 0) return;
+    } else
+        flip = radix_sort_suffix_keys(c, T3, k <= 16 ? QL : nullptr, N, k, keyA, keyB, posA, posB);
     uint64_t *keys = flip ? keyB : keyA, *keys_alt = flip ? keyA : keyB;
     uint32_t *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
 
@@ -785,9 +802,10 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     G.T3 = T3; G.QL = QL; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
     G.group_cap = (uint32_t)c->opt_group_cap;
+    G.prev_key = prev_key; G.has_prev = has_prev;
 
     int parity = 0, depth = 0, ksym = k, level = 0;
-    uint32_t m = (uint32_t)N;
+    uint32_t m = (uint32_t)n_sort;
     while (true) {
         BFQ_CUDA(cudaMemsetAsync(dcount, 0, 16, st));
         G.pos = pos; G.m = m; G.level0 = level == 0; G.ksym = ksym; G.depth0 = depth;

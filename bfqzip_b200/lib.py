@@ -176,6 +176,26 @@ class BfqGpu:
                                             _ptr(d_out_quals), C.byref(st)))
         return st.as_dict()
 
+    # ---- one collection over several GPUs (bfq_dist_build / bfq_dist_place)
+    def dist_build(self, d_bases, d_quals, d_off, nreads, total_bases, params: Params, rank, world, capacity,
+                   text_bounds, d_bwt, d_qs, d_lcp, d_keys, d_vals):
+        st = Stats()
+        tb = np.ascontiguousarray(text_bounds, np.uint64)
+        assert len(tb) == world + 1
+        n_local = C.c_uint64(0); row_base = C.c_uint64(0)
+        counts = np.zeros(world, np.uint64)
+        self._chk(self.lib.bfq_dist_build(self.h, _ptr(d_bases), _ptr(d_quals), _ptr(d_off), C.c_uint64(nreads),
+                                          C.c_uint64(total_bases), C.byref(params), C.c_int(rank), C.c_int(world),
+                                          C.c_uint64(capacity), _ptr(tb), _ptr(d_bwt), _ptr(d_qs), _ptr(d_lcp),
+                                          _ptr(d_keys), _ptr(d_vals), C.byref(n_local), C.byref(row_base),
+                                          _ptr(counts), C.byref(st)))
+        return int(n_local.value), int(row_base.value), counts, st.as_dict()
+
+    def dist_place(self, d_keys, d_vals, count, text_lo, d_off, read_lo, read_hi, d_out_bases, d_out_quals):
+        self._chk(self.lib.bfq_dist_place(self.h, _ptr(d_keys), _ptr(d_vals), C.c_uint64(count), C.c_uint64(text_lo),
+                                          _ptr(d_off), C.c_uint64(read_lo), C.c_uint64(read_hi), _ptr(d_out_bases),
+                                          _ptr(d_out_quals)))
+
     # ---- test hooks
     def debug_sort_pairs(self, keys, vals, bits):
         keys = np.ascontiguousarray(keys, np.uint64).copy(); vals = np.ascontiguousarray(vals, np.uint32).copy()

@@ -118,6 +118,27 @@ int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_qual
                      const bfq_params *params, uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp,
                      uint8_t *d_out_bases, uint8_t *d_out_quals, bfq_stats *stats);
 
+/* ---- one collection over several GPUs (second row) ----------------
+ * Every rank holds the whole collection (device pointers as in bfq_pipeline_dev) and builds the
+ * slice [row_base, row_base + n_local) of the global eBWT / QS / LCP: the suffixes whose first four
+ * symbols fall in the rank's range (ranges are derived identically on every rank, no exchange).
+ * The slice is smoothed locally (exact for -k >= 4) and leaves as (text position, base | quality << 8)
+ * pairs sorted by position; send_counts[d] of them belong to the rank that rebuilds text positions
+ * [text_bounds[d], text_bounds[d + 1]).  After the all-to-all (the caller's: NCCL, MPI ...)
+ * bfq_dist_place writes reads [read_lo, read_hi) -- text positions [text_lo, text_lo + count) -- in
+ * input order.  Together they replace eGap + bfq_ext on one collection (BFQzip_ext.py:173-196).
+ * d_bwt/d_qs/d_lcp/d_keys/d_vals hold `capacity` entries; BFQ_ECAPACITY if the slice is larger.
+ * text_bounds, n_local, row_base, send_counts (world entries) and stats are host pointers;
+ * stats counters are this rank's share (sum them over ranks). */
+int bfq_dist_build(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                   uint64_t nreads, uint64_t total_bases, const bfq_params *params, int rank, int world,
+                   uint64_t capacity, const uint64_t *text_bounds, uint8_t *d_bwt, uint8_t *d_qs,
+                   uint8_t *d_lcp, uint32_t *d_keys, uint16_t *d_vals, uint64_t *n_local,
+                   uint64_t *row_base, uint64_t *send_counts, bfq_stats *stats);
+int bfq_dist_place(bfq_ctx *ctx, uint32_t *d_keys, uint16_t *d_vals, uint64_t count, uint64_t text_lo,
+                   const uint64_t *d_off, uint64_t read_lo, uint64_t read_hi, uint8_t *d_out_bases,
+                   uint8_t *d_out_quals);
+
 /* ---- introspection ---------------------------------------------------------------------- */
 /* After a smooth_rebuild/pipeline call: the per-row state the reference keeps in
  * tmp/bwt_qs_<p>.aux and BWT_MOD/rbv (bfq_ext.cpp:555-556, 810-811), in global row order.

@@ -1,0 +1,68 @@
+"""Single-collection mode over several GPUs (bfq_dist_build / bfq_dist_place, bfqzip_b200/dist.py): the ranks'
+slices and rebuilt read ranges, put together, must be bit-identical to the oracle on the whole collection.
+On one GPU the ranks run one after the other (dist.emulate_ranks); the 2-GPU run is scripts/dist_check.py."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from bfqzip_b200 import dist, lib, synth
+
+pytestmark = pytest.mark.gpu
+STAT_KEYS = ("clusters", "discarded", "ambiguous", "processed", "bases_inside", "qs_smoothed", "modified", "nreads")
+
+
+def check(reads, M, B, world, eos=0, K=16, options=None):
+    bases, quals, off = reads
+    eng = dist.GpuEngine(M, B, 0, options)
+    try:
+        bwt, qs, lcp, ob, oq, st = dist.emulate_ranks(eng, reads, lib.default_params(eos=eos, K=K), world)
+    finally:
+        eng.close()
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, eos)
+    assert np.array_equal(bwt, rb) and np.array_equal(qs, rq)
+    assert np.array_equal(lcp, rl)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B, eos=eos, K=K))
+    assert np.array_equal(ob, eb) and np.array_equal(oq, eq)
+    assert all(st[k] == est[k] for k in STAT_KEYS)
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
+def test_dist_matches_oracle(world):
+    check(synth.make_reads(20000, 100, 900 + world), 2, 0, world)
+
+
+@pytest.mark.parametrize("mode", [(0, 1), (1, 0), (3, 1)], ids=lambda m: f"M{m[0]}B{m[1]}")
+def test_dist_modes(mode):
+    check(synth.make_reads(12000, 80, 77), mode[0], mode[1], 3)
+
+
+def test_dist_variable_length_and_duplicates():
+    g = np.load(os.path.join(H.GOLDEN, "syn_var_dup.npz"))
+    check((g["bases"], g["quals"], g["off"]), 3, 1, 4, eos=35)
+
+
+def test_dist_small_k_and_deferred_groups():
+    # -k 4 is the smallest context the mode accepts; a tiny group cap forces the deferred levels inside every slice
+    reads = synth.make_reads(6000, 60, 5)
+    check(reads, 2, 0, 2, K=4)
+    check(reads, 2, 0, 3, options={"group_cap": 8})
+
+
+def test_dist_more_ranks_than_work():
+    rng = np.random.default_rng(3)
+    bases = rng.choice(np.frombuffer(b"ACGT", np.uint8), 5 * 30).astype(np.uint8)
+    quals = rng.integers(40, 70, 150).astype(np.uint8)
+    off = (np.arange(6) * 30).astype(np.uint64)
+    check((bases, quals, off), 2, 0, 8)
+
+
+def test_dist_refuses_k_below_4():
+    reads = synth.make_reads(1000, 50, 1)
+    eng = dist.GpuEngine(2, 0, 0)
+    try:
+        with pytest.raises(lib.BfqError):
+            dist.emulate_ranks(eng, reads, lib.default_params(eos=0, K=3), 2)
+    finally:
+        eng.close()
