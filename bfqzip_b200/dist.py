@@ -106,7 +106,12 @@ def exchange_pairs(keys, vals, counts: np.ndarray, group=None):
     rkeys = torch.empty(sum(rc) + 16, dtype=keys.dtype, device=keys.device)
     rvals = torch.empty(sum(rc) + 16, dtype=vals.dtype, device=vals.device)
     dist.all_to_all_single(rkeys[:sum(rc)], keys[:sum(sc)].contiguous(), rc, sc, group=group)
-    dist.all_to_all_single(rvals[:sum(rc)], vals[:sum(sc)].contiguous(), rc, sc, group=group)
+    # 16-bit integers are not a collective type (NCCL, gloo): the payload travels as bytes
+    dist.all_to_all_single(rvals[:sum(rc)].view(torch.uint8), vals[:sum(sc)].contiguous().view(torch.uint8),
+                           [2 * x for x in rc], [2 * x for x in sc], group=group)
+    if rkeys.is_cuda:
+        # the engine works on its own stream: the received pairs must have landed before it reads them
+        torch.cuda.current_stream(rkeys.device).synchronize()
     return rkeys, rvals, sum(rc)
 
 
