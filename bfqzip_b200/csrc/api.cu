@@ -47,9 +47,9 @@ static void check_reads_dev(bfq_ctx *c, const uint64_t *d_off, uint64_t nreads, 
         len_range_kernel<<<grid, 256, 0, c->stream>>>(d_off, nreads, d);
         c->launches++;
     }
-    BFQ_CUDA(cudaMemcpyAsync((char *)c->h_small + 3072, d, 32, cudaMemcpyDeviceToHost, c->stream));
-    BFQ_CUDA(cudaMemcpyAsync((char *)c->h_small + 3072 + 32, d_off + nreads, 8, cudaMemcpyDeviceToHost, c->stream));
-    BFQ_CUDA(cudaMemcpyAsync((char *)c->h_small + 3072 + 40, d_off, 8, cudaMemcpyDeviceToHost, c->stream));
+    fetch_small(c, (char *)c->h_small + 3072, d, 32);
+    fetch_small(c, (char *)c->h_small + 3072 + 32, d_off + nreads, 8);
+    fetch_small(c, (char *)c->h_small + 3072 + 40, d_off, 8);
     BFQ_CUDA(cudaStreamSynchronize(c->stream));
     const unsigned long long *h = (const unsigned long long *)((char *)c->h_small + 3072);
     if (h[2]) BFQ_FAIL(BFQ_EINVAL, "read offsets are not non-decreasing");
@@ -114,17 +114,22 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
         build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, P->eos_byte, d_bwt, d_qs, d_lcp, d_sa, d_t3);
         c->arena.release(mk);        // sort scratch is dead (stream-ordered) once the gather is queued
     }
+    c->trace("part A done", c->stream);
     if (h_bwt || h_qs || h_lcp) {
         // the three files are final: copy them out on the side stream while parts B and C run
         BFQ_CUDA(cudaEventRecord(c->ev_a, c->stream));
         BFQ_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_a, 0));
-        if (h_bwt) BFQ_CUDA(cudaMemcpyAsync(h_bwt, d_bwt, N, cudaMemcpyDeviceToHost, c->copy_stream));
-        if (h_qs) BFQ_CUDA(cudaMemcpyAsync(h_qs, d_qs, N, cudaMemcpyDeviceToHost, c->copy_stream));
-        if (h_lcp) BFQ_CUDA(cudaMemcpyAsync(h_lcp, d_lcp, N, cudaMemcpyDeviceToHost, c->copy_stream));
+        if (!(c->sink && c->sink->files_copied)) {             // else: they left slice by slice during the group kernel
+            if (h_bwt) BFQ_CUDA(cudaMemcpyAsync(h_bwt, d_bwt, N, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (h_qs) BFQ_CUDA(cudaMemcpyAsync(h_qs, d_qs, N, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (h_lcp) BFQ_CUDA(cudaMemcpyAsync(h_lcp, d_lcp, N, cudaMemcpyDeviceToHost, c->copy_stream));
+        }
         BFQ_CUDA(cudaEventRecord(c->ev_copy, c->copy_stream));
+        c->trace("files on host (copy stream)", c->copy_stream);
     }
     SmoothResult S;
     smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats, d_sa, d_t3);
+    c->trace("part B done", c->stream);
     if (S.nreads != nreads) BFQ_FAIL(BFQ_ECUDA, "internal error: %llu end-markers for %llu reads", (unsigned long long)S.nreads, (unsigned long long)nreads);
     if (flat) {
         unpermute_dev(c, S, d_bwt, d_sa, d_off, nreads, d_out_bases, d_out_quals);
@@ -135,7 +140,10 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
         uint64_t *d_oo = arena_alloc<uint64_t>(c, nreads + 1);
         rebuild_dev(c, S, P, nullptr, d_out_bases, d_out_quals, d_oo, nullptr);
     }
-    if (h_bwt || h_qs || h_lcp) BFQ_CUDA(cudaStreamWaitEvent(c->stream, c->ev_copy, 0));   // side copies join the main stream
+    c->trace("part C done", c->stream);
+    if (c->sink && c->sink->out_copied) { BFQ_CUDA(cudaEventRecord(c->ev_copy, c->copy_stream)); c->trace("reads on host (copy stream)", c->copy_stream); }
+    if (h_bwt || h_qs || h_lcp || (c->sink && c->sink->out_copied))
+        BFQ_CUDA(cudaStreamWaitEvent(c->stream, c->ev_copy, 0));                             // side copies join the main stream
     BFQ_CUDA(cudaStreamSynchronize(c->stream));
     remember(c, S, d_bwt);
 }
@@ -222,17 +230,30 @@ int bfq_pipeline(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const
 {
     API_BEGIN
     if (!params || !off || (nreads && (!bases || !quals || !out_bases || !out_quals))) BFQ_FAIL(BFQ_EINVAL, "bfq_pipeline: null pointer");
-    const uint64_t total = host_check_off(off, nreads), N = total + nreads;
     if (stats) memset(stats, 0, sizeof *stats);
-    if (N == 0) return BFQ_OK;
+    if (nreads == 0) { host_check_off(off, nreads); return BFQ_OK; }
+    // off[nreads] is the size the caller vouches for; the full validation of the offsets runs on the host while the
+    // reads are already on their way to the device
+    const uint64_t total = off[nreads], N = total + nreads;
+    ctx->trace("call start", ctx->stream);
     uint8_t *d_b = to_device(ctx, bases, total), *d_q = to_device(ctx, quals, total);
     uint64_t *d_o = to_device(ctx, off, nreads + 1);
+    ctx->trace("inputs on device", ctx->stream);
+    host_check_off(off, nreads);
     uint8_t *d_bwt = arena_alloc<uint8_t>(ctx, N + 64), *d_qs = arena_alloc<uint8_t>(ctx, N + 64), *d_lcp = arena_alloc<uint8_t>(ctx, N + 64);
     uint8_t *d_ob = arena_alloc<uint8_t>(ctx, total + 64), *d_oq = arena_alloc<uint8_t>(ctx, total + 64);
+    bfq_ctx::HostSink sink;
+    sink.bwt = bwt; sink.qs = qs; sink.lcp = lcp; sink.out_b = out_bases; sink.out_q = out_quals; sink.off = off;
+    struct SinkScope { bfq_ctx *c; ~SinkScope() { c->sink = nullptr; } } scope{ctx};
+    ctx->sink = &sink;
     pipeline_dev(ctx, d_b, d_q, d_o, nreads, total, params, d_bwt, d_qs, d_lcp, d_ob, d_oq, stats, bwt, qs, lcp);
-    BFQ_CUDA(cudaMemcpyAsync(out_bases, d_ob, total, cudaMemcpyDeviceToHost, ctx->stream));
-    BFQ_CUDA(cudaMemcpyAsync(out_quals, d_oq, total, cudaMemcpyDeviceToHost, ctx->stream));
-    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (!sink.out_copied) {
+        BFQ_CUDA(cudaMemcpyAsync(out_bases, d_ob, total, cudaMemcpyDeviceToHost, ctx->stream));
+        BFQ_CUDA(cudaMemcpyAsync(out_quals, d_oq, total, cudaMemcpyDeviceToHost, ctx->stream));
+        BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->trace("call end", ctx->stream);
+    ctx->trace_dump();
     API_END
 }
 

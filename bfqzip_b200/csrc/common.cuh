@@ -106,11 +106,43 @@ struct bfq_ctx {
     size_t l2_window_max = 0;         // largest access-policy window
     cudaStream_t stream = nullptr;
     cudaStream_t own_stream = nullptr;
+    // Host destinations of the current host-buffer call (bfq_pipeline): stages copy finished row / read ranges out on
+    // the side stream while later stages still run, and say so in the *_copied flags.
+    struct HostSink {
+        uint8_t *bwt = nullptr, *qs = nullptr, *lcp = nullptr, *out_b = nullptr, *out_q = nullptr;
+        const uint64_t *off = nullptr;       // host copy of the read offsets
+        bool files_copied = false, out_copied = false;
+    } *sink = nullptr;
+    // option "trace": timed events at stage boundaries of a host-buffer call, printed to stderr when it ends
+    int opt_trace = 0;
+    int opt_host_slices = 16;         // option "host_slices": slices of the group kernel in a host-buffer call (1 = off)
+    std::vector<std::pair<const char *, cudaEvent_t>> trace_events;
+    void trace(const char *name, cudaStream_t s)
+    {
+        if (!opt_trace) return;
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        cudaEventRecord(e, s);
+        trace_events.emplace_back(name, e);
+    }
+    void trace_dump()
+    {
+        if (trace_events.empty()) return;
+        cudaDeviceSynchronize();
+        for (auto &p : trace_events) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, trace_events[0].second, p.second);
+            fprintf(stderr, "[bfq trace] %8.3f ms  %s\n", ms, p.first);
+        }
+        for (auto &p : trace_events) cudaEventDestroy(p.second);
+        trace_events.clear();
+    }
     cudaStream_t copy_stream = nullptr;   // D2H of the part-A files overlaps parts B and C
     cudaEvent_t ev_a = nullptr, ev_copy = nullptr;
     bfq::Arena arena;
     // host pinned scratch for small read-backs
-    uint64_t *h_small = nullptr;      // 4 KiB pinned
+    void *h_small_dev = nullptr;      // device view of h_small
+    uint64_t *h_small = nullptr;      // 4 KiB pinned (mapped: fetch_small writes it from a kernel)
     uint64_t *d_small = nullptr;      // 4 KiB device
     // options
     int opt_initial_k = 0;
@@ -165,6 +197,12 @@ struct EbwtDev {                 // device results of part A
     uint8_t *bwt = nullptr, *qs = nullptr, *lcp = nullptr;
     uint64_t n = 0;
 };
+
+// ctx.cu
+// Small results (counters, histograms) come back through a kernel that stores into the context's mapped pinned block
+// instead of a device-to-host copy: a copy would queue on the copy engine BEHIND the bulk copies of the side stream
+// and serialise the pipeline with them.  host_dst must lie inside c->h_small; bytes is a multiple of 4.
+void fetch_small(bfq_ctx *c, void *host_dst, const void *dev_src, size_t bytes);
 
 // sufsort.cu
 struct KeyRange {                // single-collection mode: this rank builds only its slice of the global eBWT

@@ -5,6 +5,22 @@
 
 namespace bfq {
 
+__global__ void fetch_small_kernel(uint32_t *__restrict__ host_dst, const uint32_t *__restrict__ src, uint32_t words)
+{
+    for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) host_dst[i] = src[i];
+}
+
+void fetch_small(bfq_ctx *c, void *host_dst, const void *dev_src, size_t bytes)
+{
+    if (!c->h_small_dev || (bytes & 3) || (char *)host_dst < (char *)c->h_small || (char *)host_dst + bytes > (char *)c->h_small + 4096) {
+        BFQ_CUDA(cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+        return;
+    }
+    uint32_t *dst = (uint32_t *)((char *)c->h_small_dev + ((char *)host_dst - (char *)c->h_small));
+    fetch_small_kernel<<<1, 256, 0, c->stream>>>(dst, (const uint32_t *)dev_src, (uint32_t)(bytes / 4));
+    BFQ_CUDA(cudaGetLastError());
+}
+
 static thread_local char g_err[1024] = "";
 
 void set_error(const char *fmt, ...)
@@ -161,7 +177,8 @@ int bfq_ctx_create(bfq_ctx **out, int device)
         BFQ_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         BFQ_CUDA(cudaEventCreateWithFlags(&c->ev_a, cudaEventDisableTiming));
         BFQ_CUDA(cudaEventCreateWithFlags(&c->ev_copy, cudaEventDisableTiming));
-        BFQ_CUDA(cudaMallocHost(&c->h_small, 4096));
+        BFQ_CUDA(cudaHostAlloc(&c->h_small, 4096, cudaHostAllocMapped));
+        if (cudaHostGetDevicePointer(&c->h_small_dev, c->h_small, 0) != cudaSuccess) { cudaGetLastError(); c->h_small_dev = nullptr; }
         BFQ_CUDA(cudaMalloc(&c->d_small, 4096));
     } catch (Error &er) {
         delete c;
@@ -198,6 +215,8 @@ int bfq_ctx_set_option(bfq_ctx *c, const char *key, int64_t value)
     else if (k == "rebuild") { if (value < 0 || value > 2) { set_error("rebuild must be 0 (auto), 1 (un-permute) or 2 (LF walk)"); return BFQ_EINVAL; } c->opt_rebuild = (int)value; }
     else if (k == "flat_min_rows") { if (value < 0) { set_error("flat_min_rows must be >= 0"); return BFQ_EINVAL; } c->opt_flat_min_rows = value; }
     else if (k == "profile") c->opt_profile = value ? 1 : 0;
+    else if (k == "trace") c->opt_trace = value ? 1 : 0;
+    else if (k == "host_slices") c->opt_host_slices = (int)std::max<int64_t>(1, std::min<int64_t>(value, 64));
     else { set_error("unknown option '%s'", key); return BFQ_EINVAL; }
     return BFQ_OK;
 }

@@ -508,7 +508,7 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
         rs_scan_chunks_kernel<<<1, 1024, 0, st>>>(cc, cb, nchunks, (uint32_t *)(d_prev + 1));
         BFQ_CUDA(cudaGetLastError());
     }
-    BFQ_CUDA(cudaMemcpyAsync(c->h_small, d_prev, 16, cudaMemcpyDeviceToHost, st));
+    fetch_small(c, c->h_small, d_prev, 16);
     BFQ_CUDA(cudaStreamSynchronize(st));
     const uint64_t pk = c->h_small[0];
     const uint64_t cnt = (uint32_t)c->h_small[1];

@@ -20,9 +20,9 @@ struct WalkHdr { uint32_t cnt[5]; uint32_t plane[3]; };
 __global__ void __launch_bounds__(256)
 walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase, uint32_t nreads,
             int max_len, uint64_t code2byte, const uint64_t *__restrict__ off_known,
-            uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q, uint32_t *__restrict__ lens)
+            uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q, uint32_t *__restrict__ lens, uint32_t g0 = 0)
 {
-    const uint32_t g = blockIdx.x * 256u + threadIdx.x;
+    const uint32_t g = g0 + blockIdx.x * 256u + threadIdx.x;
     if (g >= nreads) return;
     uint64_t row = g;
     uint64_t wpos;            // next write index
@@ -301,10 +301,30 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P, const u
     uint64_t c2b = 0;
     for (int k = 0; k < 8; k++) c2b |= (uint64_t)S.alpha.code2byte[k] << (8 * k);
     if (d_off_known) {
-        ProfScope ps(c, PC_WALK, (S.n - R) * (64 + 2));
-        walk_kernel<<<div_up(R, 256), 256, 0, st>>>(S.lines, S.obase, (uint32_t)R, P->max_len, c2b, d_off_known,
-                                                    d_out_bases, d_out_quals, nullptr);
-        BFQ_CUDA(cudaGetLastError());
+        bfq_ctx::HostSink *sink = c->sink;
+        // Host-buffer call: the walk runs one GPU-full of reads at a time (a read is one thread, so a slice of resident
+        // size costs nothing) and every slice's reads leave for the host while the next slice walks.
+        const uint64_t wave = (uint64_t)c->num_sms * 2048;
+        const bool sliced = sink && sink->out_b && sink->out_q && sink->off && R >= 2 * wave;
+        const uint64_t step = sliced ? wave : R;
+        for (uint64_t g0 = 0; g0 < R; g0 += step) {
+            const uint64_t g1 = std::min(R, g0 + step);
+            {
+                ProfScope ps(c, PC_WALK, (S.n - R) * (64 + 2) * (g1 - g0) / R);
+                walk_kernel<<<div_up(g1 - g0, 256), 256, 0, st>>>(S.lines, S.obase, (uint32_t)g1, P->max_len, c2b, d_off_known,
+                                                                 d_out_bases, d_out_quals, nullptr, (uint32_t)g0);
+                BFQ_CUDA(cudaGetLastError());
+            }
+            if (sliced) {
+                // walk_kernel writes exactly the bytes of its own read, so [off[g0], off[g1]) is final here
+                const uint64_t lo = sink->off[g0], hi = sink->off[g1];
+                BFQ_CUDA(cudaEventRecord(c->ev_a, st));
+                BFQ_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_a, 0));
+                BFQ_CUDA(cudaMemcpyAsync(sink->out_b + lo, d_out_bases + lo, hi - lo, cudaMemcpyDeviceToHost, c->copy_stream));
+                BFQ_CUDA(cudaMemcpyAsync(sink->out_q + lo, d_out_quals + lo, hi - lo, cudaMemcpyDeviceToHost, c->copy_stream));
+                sink->out_copied = true;
+            }
+        }
         return;
     }
     Arena::Mark mk = c->arena.mark();
@@ -329,7 +349,7 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P, const u
         BFQ_CUDA(cudaGetLastError());
     }
     if (total_out) {
-        BFQ_CUDA(cudaMemcpyAsync(c->h_small, blk + nblk, 8, cudaMemcpyDeviceToHost, st));
+        fetch_small(c, c->h_small, blk + nblk, 8);
         BFQ_CUDA(cudaStreamSynchronize(st));
         *total_out = c->h_small[0];
     } else {

@@ -774,7 +774,7 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
         else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, d_t3);
         launch_check(c);
     }
-    BFQ_CUDA(cudaMemcpyAsync(c->h_small, d_stats, (ST_COUNT + 2) * 8, cudaMemcpyDeviceToHost, st));
+    fetch_small(c, c->h_small, d_stats, (ST_COUNT + 2) * 8);
     BFQ_CUDA(cudaStreamSynchronize(st));
     const uint64_t *h = c->h_small;
     const uint32_t *cnts = (const uint32_t *)(h + ST_COUNT);

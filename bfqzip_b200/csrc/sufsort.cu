@@ -57,7 +57,7 @@ void byte_histogram(bfq_ctx *c, const uint8_t *d_data, uint64_t n, uint64_t hist
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, 256 * 16) + 1);
         hist256_kernel<<<grid, 256, 0, c->stream>>>(d_data, n, d_hist);
     }
-    BFQ_CUDA(cudaMemcpyAsync(c->h_small, d_hist, 256 * 8, cudaMemcpyDeviceToHost, c->stream));
+    fetch_small(c, c->h_small, d_hist, 256 * 8);
     BFQ_CUDA(cudaStreamSynchronize(c->stream));
     for (int i = 0; i < 256; i++) hist_out[i] = c->h_small[i];
 }
@@ -151,6 +151,7 @@ struct GroupTileArgs {
     uint32_t *defer_count;      // [0] groups deferred, [1] members (filled by defer_len_kernel)
     uint32_t *defer_start;      // list index of the head of every deferred group
     uint32_t defer_cap;
+    uint32_t tile0;             // first tile of this launch (level 0 may be launched in slices)
     uint64_t prev_key;          // level 0 of a key range: key of the global row just before this list (has_prev)
     int has_prev;
     uint64_t kmask;             // key bits that take part in group equality (level 0: the 3*ksym symbol bits)
@@ -454,7 +455,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     __shared__ uint32_t s_ngroups, s_next;
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const uint32_t t0 = blockIdx.x * (uint32_t)GT_T;
+    const uint32_t t0 = (A.tile0 + blockIdx.x) * (uint32_t)GT_T;
     const uint32_t m = A.m;
     const int ksym = A.ksym;
     const int depth = A.depth0 + ksym;
@@ -696,9 +697,31 @@ static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgs &A)
 {
     const size_t smem = group_tile_smem(A.W);
     BFQ_CUDA(cudaFuncSetAttribute(group_tile_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ProfScope ps(c, PC_GROUP, (uint64_t)A.m * (sizeof(K) + 4 + 3 + 4 * (uint64_t)A.W));
-    group_tile_kernel<K><<<div_up(A.m, GT_T), GT_THREADS, smem, c->stream>>>(keys, A);
-    BFQ_CUDA(cudaGetLastError());
+    const uint32_t ntiles = div_up(A.m, GT_T);
+    bfq_ctx::HostSink *sink = c->sink;
+    // host-buffer call: the finished rows leave for the host slice by slice while the next slice is ordered
+    const uint32_t nslices = (sink && A.level0 && A.bwt && (sink->bwt || sink->qs || sink->lcp) && ntiles >= 4096) ? (uint32_t)c->opt_host_slices : 1;
+    const uint32_t per = div_up(ntiles, nslices);
+    for (uint32_t s = 0; s < nslices; s++) {
+        GroupTileArgs B = A;
+        B.tile0 = s * per;
+        const uint32_t cnt = std::min(per, ntiles - B.tile0);
+        {
+            ProfScope ps(c, PC_GROUP, (uint64_t)cnt * GT_T * (sizeof(K) + 4 + 3 + 4 * (uint64_t)A.W));
+            group_tile_kernel<K><<<cnt, GT_THREADS, smem, c->stream>>>(keys, B);
+            BFQ_CUDA(cudaGetLastError());
+        }
+        if (nslices > 1) {
+            // rows below the slice end are final unless a group was deferred (then everything is copied again later)
+            const uint64_t lo = (uint64_t)B.tile0 * GT_T, hi = std::min<uint64_t>(A.m, (uint64_t)(B.tile0 + cnt) * GT_T);
+            BFQ_CUDA(cudaEventRecord(c->ev_a, c->stream));
+            BFQ_CUDA(cudaStreamWaitEvent(c->copy_stream, c->ev_a, 0));
+            if (sink->bwt) BFQ_CUDA(cudaMemcpyAsync(sink->bwt + lo, A.bwt + lo, hi - lo, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (sink->qs) BFQ_CUDA(cudaMemcpyAsync(sink->qs + lo, A.qs + lo, hi - lo, cudaMemcpyDeviceToHost, c->copy_stream));
+            if (sink->lcp) BFQ_CUDA(cudaMemcpyAsync(sink->lcp + lo, A.lcp + lo, hi - lo, cudaMemcpyDeviceToHost, c->copy_stream));
+            sink->files_copied = true;
+        }
+    }
 }
 
 size_t packed_text_words(uint64_t N) { return ((N + 320 + 63) / 64) * 3 + 2; }
@@ -751,6 +774,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         BFQ_CUDA(cudaGetLastError());
     }
 
+    c->trace("text packed", st);
     // ---- level 0: global sort on k symbols, groups finished in shared memory
     int k = c->opt_initial_k;
     if (k <= 0) k = 16;
@@ -768,6 +792,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     uint64_t *keys = flip ? keyB : keyA, *keys_alt = flip ? keyA : keyB;
     uint32_t *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
 
+    c->trace("suffix keys sorted", st);
     // The packed text is what every group gathers from at random: pin it in L2 (persisting access
     // window, set aside only for the group kernels) while the sorted list streams through; T3 of config 2 is 38 MB of the 126 MB L2.
     const size_t t3_bytes = (ngroups * 3 + 2) * 8;
@@ -816,10 +841,11 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         G.g_off = level ? dtab[parity ^ 1][3] : nullptr;
         G.defer_start = dtab[parity][0];
         launch_group_tile<uint64_t>(c, keys, G);
-        BFQ_CUDA(cudaMemcpyAsync(c->h_small, dcount, 4, cudaMemcpyDeviceToHost, st));
+        fetch_small(c, c->h_small, dcount, 4);
         BFQ_CUDA(cudaStreamSynchronize(st));
         const uint32_t ndef = ((uint32_t *)c->h_small)[0];
         if (ndef == 0) break;
+        if (c->sink) c->sink->files_copied = false;      // deferred groups rewrite rows that already left
         if (ndef > dcap) BFQ_FAIL(BFQ_ECUDA, "internal error: %u deferred groups exceed the table of %u", ndef, dcap);
         if (++level > 64) BFQ_FAIL(BFQ_ECUDA, "suffix sort did not converge (internal error)");
         // ---- next level: the members of the deferred groups, keyed by (group, next s symbols)
@@ -831,7 +857,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
             scan_excl_u32_kernel<<<1, 1024, 0, st>>>(dlen, doff, ndef, dcount + 1);
             BFQ_CUDA(cudaGetLastError());
         }
-        BFQ_CUDA(cudaMemcpyAsync(c->h_small, dcount + 1, 4, cudaMemcpyDeviceToHost, st));
+        fetch_small(c, c->h_small, dcount + 1, 4);
         BFQ_CUDA(cudaStreamSynchronize(st));
         const uint32_t m2 = ((uint32_t *)c->h_small)[0];
         depth += ksym;

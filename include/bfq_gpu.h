@@ -83,7 +83,12 @@ void bfq_ctx_destroy(bfq_ctx *ctx);
  *   "rebuild"     part C of the fused pipeline: 0 auto, 1 streaming un-permute through the suffix array, 2 inverse-LF walk
  *   "flat_min_rows" auto mode switches to the un-permute from this many BWT rows on
  *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
- *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)      */
+ *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)
+ *   "host_slices" host-buffer calls (bfq_pipeline) launch the group kernel in this many slices and
+ *                 copy every finished slice of .bwt/.bwt.qs/.1.lcp rows to the host while the next
+ *                 one runs (default 16, 1 = one launch and one copy); the rebuilt reads leave the
+ *                 same way, one GPU-full of reads at a time
+ *   "trace"       1 = print a timeline of the stage boundaries of every bfq_pipeline call to stderr */
 int  bfq_ctx_set_option(bfq_ctx *ctx, const char *key, int64_t value);
 /* Run on a caller-owned CUDA stream (a cudaStream_t cast to void*) instead of the context's own,
  * so that the caller's events bracket the library's kernels.  NULL restores the own stream. */

@@ -252,3 +252,24 @@ def test_pipeline_roundtrip_1M():
     assert changed <= st["qs_smoothed"]
     assert set(np.unique(oq[oq != quals]).tolist()) <= {ord(">")}
     assert lcp[0] == 0 and int(lcp.max()) <= 100
+    # the host-buffer call hands finished rows / reads to the host slice by slice while later slices still run
+    # (pageable and pinned destinations): it must return exactly what the device-buffer call leaves in HBM
+    import torch
+    dev = torch.device("cuda", 0)
+    g = ctx(2, 0)
+    d = lambda a: torch.from_numpy(a).to(dev)
+    e = lambda k: torch.empty(k + 64, dtype=torch.uint8, device=dev)
+    total = len(bases)
+    d_bwt, d_qs, d_lcp, d_ob, d_oq = e(n), e(n), e(n), e(total), e(total)
+    st2 = g.pipeline_dev(d(bases), d(quals), d(off.view(np.int64)), 1_000_000, total, lib.default_params(eos=0), d_bwt, d_qs, d_lcp, d_ob, d_oq)
+    assert st2 == st
+    for host, devt in ((bwt, d_bwt), (qs, d_qs), (lcp, d_lcp), (ob, d_ob), (oq, d_oq)):
+        assert np.array_equal(host, devt[:len(host)].cpu().numpy())
+    for slices in (1, 7):
+        g.set_option("host_slices", slices)
+        try:
+            (b2, q2, l2), (ob2, oq2), st3 = g.pipeline(bases, quals, off, lib.default_params(eos=0))
+        finally:
+            g.set_option("host_slices", 16)
+        assert st3 == st and np.array_equal(b2, bwt) and np.array_equal(q2, qs) and np.array_equal(l2, lcp)
+        assert np.array_equal(ob2, ob) and np.array_equal(oq2, oq)
