@@ -15,7 +15,7 @@ single-GPU pipeline on the same FASTQ -- one eBWT, one set of clusters -- and th
   5. the owner sorts what it received back into text order and writes its reads.
 
 Engines: ``GpuEngine`` drives the C ABI (bfq_dist_build / bfq_dist_place).  The orchestration takes any object with
-the same two methods, which is how the CPU tests run it over gloo with a stand-in built from the oracle.
+the same methods, which is how the CPU tests run the exchange over gloo with a stand-in engine and no GPU.
 """
 from __future__ import annotations
 
