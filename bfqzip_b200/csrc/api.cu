@@ -290,11 +290,15 @@ int bfq_dist_build(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals,
     if (N == 0) return BFQ_OK;
     KeyRange R;
     R.rank = rank; R.world = world; R.capacity = capacity;
-    uint32_t *d_sa = arena_alloc<uint32_t>(c, capacity + 16);
+    // text positions take 64 bits from 2^32 rows on; the rows of one rank stay 32-bit indexed
+    const bool wide = c->opt_wide_positions || N >= ((uint64_t)1 << 32) - 64;
+    if (capacity >= ((uint64_t)1 << 32) - 64) BFQ_FAIL(BFQ_ETOOLARGE, "capacity of %llu rows; one GPU indexes its rows with 32 bits", (unsigned long long)capacity);
+    void *d_sa = wide ? (void *)arena_alloc<uint64_t>(c, capacity + 16) : (void *)arena_alloc<uint32_t>(c, capacity + 16);
     uint64_t *d_t3 = arena_alloc<uint64_t>(c, packed_text_words(N));
     {
         Arena::Mark mk = c->arena.mark();
-        build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, params->eos_byte, d_bwt, d_qs, d_lcp, d_sa, d_t3, &R);
+        if (wide) build_ebwt_dev_wide(c, d_bases, d_quals, d_off, nreads, total_bases, mx, params->eos_byte, d_bwt, d_qs, d_lcp, (uint64_t *)d_sa, d_t3, &R);
+        else build_ebwt_dev(c, d_bases, d_quals, d_off, nreads, total_bases, mx, params->eos_byte, d_bwt, d_qs, d_lcp, (uint32_t *)d_sa, d_t3, &R);
         c->arena.release(mk);
     }
     *n_local = R.n_local; *row_base = R.row_base;
@@ -303,8 +307,8 @@ int bfq_dist_build(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals,
         memcpy(ah, c->base_hist, sizeof ah);
         ah[params->eos_byte] += nreads;
         SmoothResult S;
-        smooth_dev(c, d_bwt, d_qs, d_lcp, R.n_local, params, &S, stats, d_sa, d_t3, ah);
-        emit_sorted_pairs_dev(c, S, d_bwt, d_sa, N, text_bounds, world, d_keys, d_vals, send_counts);
+        smooth_dev(c, d_bwt, d_qs, d_lcp, R.n_local, params, &S, stats, d_sa, d_t3, ah, wide);
+        emit_sorted_pairs_dev(c, S, d_bwt, d_sa, wide, N, text_bounds, world, d_keys, d_vals, send_counts);
     }
     if (stats) { stats->n = N; stats->nreads = nreads; }
     BFQ_CUDA(cudaStreamSynchronize(c->stream));

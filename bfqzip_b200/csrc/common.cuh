@@ -115,6 +115,7 @@ struct bfq_ctx {
     } *sink = nullptr;
     // option "trace": timed events at stage boundaries of a host-buffer call, printed to stderr when it ends
     int opt_trace = 0;
+    int opt_wide_positions = 0;       // option "wide_positions": 64-bit text positions in single-collection mode even below 2^32 rows (tests)
     int opt_host_slices = 16;         // option "host_slices": slices of the group kernel in a host-buffer call (1 = off)
     std::vector<std::pair<const char *, cudaEvent_t>> trace_events;
     void trace(const char *name, cudaStream_t s)
@@ -215,6 +216,10 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
                     uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos_byte,
                     uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep = nullptr,
                     KeyRange *range = nullptr);
+void build_ebwt_dev_wide(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                         uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos_byte,
+                         uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint64_t *d_sa_out, uint64_t *d_t3_keep,
+                         KeyRange *range);       // 64-bit text positions; key ranges only
 size_t packed_text_words(uint64_t N);     // u64 words build_ebwt_dev needs for the packed text of N rows
 // smooth.cu
 struct SmoothResult {
@@ -227,7 +232,8 @@ struct SmoothResult {
 // d_sa / d_t3 (both or none): suffix array of the rows and the packed text from part A -> flat mode
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
                 uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
-                const uint32_t *d_sa = nullptr, const uint64_t *d_t3 = nullptr, const uint64_t *alpha_hist = nullptr);
+                const void *d_sa = nullptr, const uint64_t *d_t3 = nullptr, const uint64_t *alpha_hist = nullptr,
+                bool sa_wide = false);      // sa_wide: d_sa holds u64 positions (else u32)
 // alpha_hist: byte histogram that fixes the alphabet (single-collection mode: the rows are a slice of the global eBWT
 // and may miss a symbol); NULL = histogram of d_bwt itself, as buildFreq does.
 // rebuild.cu
@@ -239,19 +245,21 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P,
 // back into text order by a streaming sort on SA - 1 instead of an inverse-LF walk.  off = read offsets.
 void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa,
                    const uint64_t *d_off, uint64_t nreads, uint8_t *d_out_bases, uint8_t *d_out_quals);
-// Single-collection mode, sending side: (text position, base | quality << 8) of every local row, sorted by position;
-// send_counts[d] = pairs whose position lies in [text_bounds[d], text_bounds[d + 1]).  n_total = rows of the global eBWT.
-void emit_sorted_pairs_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa, uint64_t n_total,
+// Single-collection mode, sending side: (text position - text_bounds[d], base | quality << 8) of every local row, grouped by
+// destination d; send_counts[d] = pairs whose position lies in [text_bounds[d], text_bounds[d + 1]).  n_total = rows of the global eBWT.
+void emit_sorted_pairs_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const void *d_sa, bool sa_wide, uint64_t n_total,
                            const uint64_t *text_bounds, int world, uint32_t *d_keys, uint16_t *d_vals, uint64_t *send_counts);
-// receiving side: the pairs of text positions [t_lo, t_lo + cnt) in any order -> reads [read_lo, read_hi) in input order
+// receiving side: pairs keyed by (text position - t_lo), one per position of [t_lo, t_lo + cnt), in any order -> reads
+// [read_lo, read_hi) in input order
 void place_pairs_dev(bfq_ctx *c, uint32_t *d_keys, uint16_t *d_vals, uint64_t cnt, uint64_t t_lo, const uint64_t *d_off,
                      uint64_t read_lo, uint64_t read_hi, uint8_t *d_out_bases, uint8_t *d_out_quals);
 // radix.cu
 // Single-collection mode: the same, restricted to the suffixes whose key falls in the range of `rank` (ranges cut on
 // the first four symbols from a histogram all ranks compute identically).  n_local = suffixes of this rank,
 // row_base = rows of the global eBWT before them, prev_key / has_prev = key of the row just before the range.
+template <typename V>        // V = position type, u32 or u64 (collections of 2^32 rows and more)
 int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, int rank, int world,
-                                 uint64_t *keys_a, uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b, uint64_t capacity,
+                                 uint64_t *keys_a, uint64_t *keys_b, V *pos_a, V *pos_b, uint64_t capacity,
                                  uint64_t *n_local, uint64_t *row_base, uint64_t *prev_key, bool *has_prev);
 // Sorts (key, 16-bit payload) pairs whose keys are exactly the integers 0..n-1 in some order (applying a
 // permutation with streaming passes instead of a random scatter); the digit histograms are computed on the host.
@@ -265,6 +273,8 @@ int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, u
 // returned flag is 0, in keys_b/vals_b when 1 (ping-pong buffers, both n long).
 int radix_sort_pairs64(bfq_ctx *c, uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a,
                        uint32_t *vals_b, uint64_t n, int bits);
+int radix_sort_pairs64(bfq_ctx *c, uint64_t *keys_a, uint64_t *keys_b, uint64_t *vals_a,
+                       uint64_t *vals_b, uint64_t n, int bits);
 int radix_sort_pairs32(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a,
                        uint32_t *vals_b, uint64_t n, int bits);
 int radix_sort_pairs32_16(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a,

@@ -216,6 +216,7 @@ int bfq_ctx_set_option(bfq_ctx *c, const char *key, int64_t value)
     else if (k == "flat_min_rows") { if (value < 0) { set_error("flat_min_rows must be >= 0"); return BFQ_EINVAL; } c->opt_flat_min_rows = value; }
     else if (k == "profile") c->opt_profile = value ? 1 : 0;
     else if (k == "trace") c->opt_trace = value ? 1 : 0;
+    else if (k == "wide_positions") c->opt_wide_positions = value ? 1 : 0;
     else if (k == "host_slices") c->opt_host_slices = (int)std::max<int64_t>(1, std::min<int64_t>(value, 64));
     else { set_error("unknown option '%s'", key); return BFQ_EINVAL; }
     return BFQ_OK;

@@ -146,6 +146,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
                    S *__restrict__ status, uint32_t *__restrict__ tile_counter)
 {
     constexpr int TILE = RS_THREADS * ITEMS;
+    static_assert(sizeof(V) <= sizeof(K), "the payload is staged in the key buffer");
     constexpr int FS = StatusTraits<S>::FS;
     constexpr S VMASK = (((S)1) << FS) - 1;
 
@@ -360,7 +361,7 @@ constexpr int RS_SEL_ITEMS = 16;                      // consecutive positions p
 constexpr int RS_SEL_CHUNK = RS_THREADS * RS_SEL_ITEMS;
 
 __global__ void __launch_bounds__(RS_THREADS)
-rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint32_t n, int k, uint32_t *__restrict__ hist)
+rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint64_t n, int k, uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t sh[1 << RS_TOP_BITS];
     for (int i = threadIdx.x; i < (1 << RS_TOP_BITS); i += RS_THREADS) sh[i] = 0;
@@ -375,11 +376,11 @@ rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint32_t n, int k, uint32_t 
 
 // WRITE = false: per-chunk count of selected positions and the largest key below the range;
 // WRITE = true : ordered compaction (position order is kept: the sort relies on it for ties) + digit histograms
-template <bool WRITE>
+template <bool WRITE, typename V>
 __global__ void __launch_bounds__(RS_THREADS)
-rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k, uint64_t lo,
+rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint64_t n, int k, uint64_t lo,
                  uint64_t hi, RsPasses P, uint32_t *__restrict__ chunk_count, const uint32_t *__restrict__ chunk_base,
-                 unsigned long long *__restrict__ prev_key, uint64_t *__restrict__ keys, uint32_t *__restrict__ vals,
+                 unsigned long long *__restrict__ prev_key, uint64_t *__restrict__ keys, V *__restrict__ vals,
                  uint32_t *__restrict__ hist)
 {
     __shared__ uint32_t sh[WRITE ? RS_MAX_PASSES * RS_RADIX : 1];
@@ -426,7 +427,7 @@ rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ Q
             for (int q = 0; q < RS_MAX_PASSES; q++)
                 if (q < P.num) atomicAdd(&sh[q * RS_RADIX + digit_of(key[i], P.shift[q], (1u << P.bits[q]) - 1)], 1u);
             keys[dst] = QL ? (key[i] | ((uint64_t)QL[p] << 48)) : key[i];
-            vals[dst] = (uint32_t)p;
+            vals[dst] = (V)p;
             dst++;
         }
     }
@@ -462,11 +463,13 @@ rs_scan_chunks_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ ou
     if (tid == 0) *total = s_carry;
 }
 
+template <typename V>
 int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, int rank, int world,
-                                 uint64_t *keys_a, uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b, uint64_t capacity,
+                                 uint64_t *keys_a, uint64_t *keys_b, V *pos_a, V *pos_b, uint64_t capacity,
                                  uint64_t *n_local, uint64_t *row_base, uint64_t *prev_key, bool *has_prev)
 {
-    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    if (sizeof(V) == 4 && n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
+    if (n >= ((uint64_t)1 << 43)) BFQ_FAIL(BFQ_ETOOLARGE, "collection of %llu rows", (unsigned long long)n);
     if (3 * k < RS_TOP_BITS) BFQ_FAIL(BFQ_EINVAL, "the key-range split needs an initial key of at least 4 symbols");
     cudaStream_t st = c->stream;
     RsPasses P = plan_passes(3 * k);
@@ -483,7 +486,7 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
     {
         ProfScope ps(c, PC_KEYS, n * 3 / 8);
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
-        rs_top_hist_kernel<<<grid, RS_THREADS, 0, st>>>(T3, (uint32_t)n, k, top);
+        rs_top_hist_kernel<<<grid, RS_THREADS, 0, st>>>(T3, n, k, top);
         BFQ_CUDA(cudaGetLastError());
     }
     BFQ_CUDA(cudaMemcpyAsync(h.data(), top, h.size() * 4, cudaMemcpyDeviceToHost, st));
@@ -498,13 +501,17 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
         return 1u << RS_TOP_BITS;
     };
     const uint32_t b0 = bin_of(rank), b1 = bin_of(rank + 1);
-    uint64_t below = 0;
+    uint64_t below = 0, mine = 0;
     for (uint32_t b = 0; b < b0; b++) below += h[b];
+    for (uint32_t b = b0; b < b1; b++) mine += h[b];
+    // (the 32-bit bin counters wrap for a bin of 2^32 suffixes; such a collection fails the capacity check below)
+    if (mine >= ((uint64_t)1 << 32) - 64)
+        BFQ_FAIL(BFQ_ETOOLARGE, "rank %d of %d would sort %llu suffixes; one GPU indexes its rows with 32 bits", rank, world, (unsigned long long)mine);
     const int sh = 3 * k - RS_TOP_BITS;
     const uint64_t lo = (uint64_t)b0 << sh, hi = (uint64_t)b1 << sh;
     {
         ProfScope ps(c, PC_KEYS, n * 3 / 8, 2);
-        rs_select_kernel<false><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, (uint32_t)n, k, lo, hi, P, cc, nullptr, d_prev, nullptr, nullptr, nullptr);
+        rs_select_kernel<false, V><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, n, k, lo, hi, P, cc, nullptr, d_prev, nullptr, nullptr, nullptr);
         rs_scan_chunks_kernel<<<1, 1024, 0, st>>>(cc, cb, nchunks, (uint32_t *)(d_prev + 1));
         BFQ_CUDA(cudaGetLastError());
     }
@@ -521,14 +528,18 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
     if (cnt) {
         {
             ProfScope ps(c, PC_KEYS, n * 3 / 8 + cnt * 14);
-            rs_select_kernel<true><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, (uint32_t)n, k, lo, hi, P, nullptr, cb, nullptr, keys_a, pos_a, hist);
+            rs_select_kernel<true, V><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, n, k, lo, hi, P, nullptr, cb, nullptr, keys_a, pos_a, hist);
             BFQ_CUDA(cudaGetLastError());
         }
-        flip = radix_passes<uint64_t, uint32_t, 16>(c, keys_a, keys_b, pos_a, pos_b, cnt, P, hist);
+        flip = radix_passes<uint64_t, V, 16>(c, keys_a, keys_b, pos_a, pos_b, cnt, P, hist);
     }
     c->arena.release(mk);
     return flip;
 }
+template int radix_sort_suffix_keys_range<uint32_t>(bfq_ctx *, const uint64_t *, const uint16_t *, uint64_t, int, int, int, uint64_t *, uint64_t *,
+                                                    uint32_t *, uint32_t *, uint64_t, uint64_t *, uint64_t *, uint64_t *, bool *);
+template int radix_sort_suffix_keys_range<uint64_t>(bfq_ctx *, const uint64_t *, const uint16_t *, uint64_t, int, int, int, uint64_t *, uint64_t *,
+                                                    uint64_t *, uint64_t *, uint64_t, uint64_t *, uint64_t *, uint64_t *, bool *);
 
 int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, uint64_t n, int k, uint64_t *keys_a,
                            uint64_t *keys_b, uint32_t *pos_a, uint32_t *pos_b)
@@ -583,6 +594,10 @@ int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint1
 int radix_sort_pairs64(bfq_ctx *c, uint64_t *ka, uint64_t *kb, uint32_t *va, uint32_t *vb, uint64_t n, int bits)
 {
     return radix_sort_pairs<uint64_t, 16>(c, ka, kb, va, vb, n, bits);
+}
+int radix_sort_pairs64(bfq_ctx *c, uint64_t *ka, uint64_t *kb, uint64_t *va, uint64_t *vb, uint64_t n, int bits)
+{
+    return radix_sort_pairs<uint64_t, 16, uint64_t>(c, ka, kb, va, vb, n, bits);
 }
 int radix_sort_pairs32(bfq_ctx *c, uint32_t *ka, uint32_t *kb, uint32_t *va, uint32_t *vb, uint64_t n, int bits)
 {

@@ -211,51 +211,86 @@ void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, cons
 }
 
 // ---------------------------------------------------------------- single-collection mode over several GPUs
-__global__ void bound_counts_kernel(const uint32_t *__restrict__ keys, uint32_t n, const uint64_t *__restrict__ bounds, int world,
-                                    unsigned long long *__restrict__ lower)
+// Every smoothed row goes to the rank that rebuilds its text position.  A row becomes (destination, position relative to
+// the destination's first text position | value << 32); ONE radix pass on the destination groups them, then the two
+// halves are split into the arrays the all-to-all sends.  Relative positions fit 32 bits even when the collection does not.
+constexpr int DIST_MAX_WORLD = 255;
+
+template <typename P>
+__global__ void __launch_bounds__(256)
+emit_dest_pairs_kernel(const P *__restrict__ SA, const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qflat,
+                       const uint8_t *__restrict__ obase, uint32_t n, uint64_t n_total, const uint64_t *__restrict__ bounds,
+                       int world, uint64_t *__restrict__ dest, uint64_t *__restrict__ packed)
+{
+    __shared__ uint64_t s_b[DIST_MAX_WORLD + 1];
+    for (int d = threadIdx.x; d <= world; d += 256) s_b[d] = bounds[d];
+    __syncthreads();
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t p = (uint64_t)SA[i];
+    const uint64_t tp = p ? p - 1 : n_total - 1;         // read starts land on a terminator slot (never copied out)
+    int lo = 0, hi = world;                               // last d with s_b[d] <= tp
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_b[mid] <= tp) lo = mid; else hi = mid; }
+    const uint8_t q = qflat[i];
+    const uint8_t base = (q & 0x80) ? obase[i] : bwt[i];
+    dest[i] = (uint64_t)lo;
+    packed[i] = (tp - s_b[lo]) | ((uint64_t)(base | ((uint32_t)(q & 0x7F) << 8)) << 32);
+}
+
+__global__ void __launch_bounds__(256)
+split_pairs_kernel(const uint64_t *__restrict__ packed, uint32_t n, uint32_t *__restrict__ keys, uint16_t *__restrict__ vals)
+{
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t v = packed[i];
+    keys[i] = (uint32_t)v;
+    vals[i] = (uint16_t)(v >> 32);
+}
+
+__global__ void dest_counts_kernel(const uint64_t *__restrict__ dest, uint32_t n, int world, unsigned long long *__restrict__ lower)
 {
     const int d = threadIdx.x;
     if (d > world) return;
-    const uint64_t b = bounds[d];
-    uint32_t lo = 0, hi = n;                      // first index with key >= b
-    while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if ((uint64_t)keys[mid] < b) lo = mid + 1; else hi = mid; }
+    uint32_t lo = 0, hi = n;                      // first index with dest >= d
+    while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if (dest[mid] < (uint64_t)d) lo = mid + 1; else hi = mid; }
     lower[d] = lo;
 }
 
-__global__ void __launch_bounds__(256) rebase_keys_kernel(uint32_t *__restrict__ keys, uint64_t n, uint32_t base)
-{
-    const uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x;
-    if (i < n) keys[i] -= base;
-}
-
-void emit_sorted_pairs_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const uint32_t *d_sa, uint64_t n_total,
+void emit_sorted_pairs_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, const void *d_sa, bool sa_wide, uint64_t n_total,
                            const uint64_t *text_bounds, int world, uint32_t *d_keys, uint16_t *d_vals, uint64_t *send_counts)
 {
     cudaStream_t st = c->stream;
     const uint64_t n = S.n;
     for (int d = 0; d < world; d++) send_counts[d] = 0;
     if (n == 0) return;
-    if (world + 1 > 256) BFQ_FAIL(BFQ_EINVAL, "at most 255 ranks");
+    if (world > DIST_MAX_WORLD) BFQ_FAIL(BFQ_EINVAL, "at most %d ranks", DIST_MAX_WORLD);
+    for (int d = 0; d < world; d++)
+        if (text_bounds[d + 1] < text_bounds[d] || text_bounds[d + 1] - text_bounds[d] >= ((uint64_t)1 << 32))
+            BFQ_FAIL(BFQ_EINVAL, "text_bounds must be non-decreasing with fewer than 2^32 positions per rank");
+    if (text_bounds[0] != 0 || text_bounds[world] != n_total) BFQ_FAIL(BFQ_EINVAL, "text_bounds must cover [0, rows of the collection)");
     Arena::Mark mk = c->arena.mark();
-    uint32_t *kb = arena_alloc<uint32_t>(c, n + 16);
-    uint16_t *vb = arena_alloc<uint16_t>(c, n + 16);
+    uint64_t *da = arena_alloc<uint64_t>(c, n + 16), *db = arena_alloc<uint64_t>(c, n + 16);
+    uint64_t *pa = arena_alloc<uint64_t>(c, n + 16), *pb = arena_alloc<uint64_t>(c, n + 16);
     uint64_t *d_bounds = arena_alloc<uint64_t>(c, 2 * (world + 1));
     unsigned long long *d_lower = (unsigned long long *)(d_bounds + world + 1);
+    BFQ_CUDA(cudaMemcpyAsync(d_bounds, text_bounds, (world + 1) * 8, cudaMemcpyHostToDevice, st));
     {
-        ProfScope ps(c, PC_WALK, n * (4 + 3 + 6));
-        emit_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, d_keys, d_vals, (uint32_t)n_total);
+        ProfScope ps(c, PC_WALK, n * (4 + 3 + 16));
+        if (sa_wide)
+            emit_dest_pairs_kernel<uint64_t><<<div_up(n, 256), 256, 0, st>>>((const uint64_t *)d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, n_total, d_bounds, world, da, pa);
+        else
+            emit_dest_pairs_kernel<uint32_t><<<div_up(n, 256), 256, 0, st>>>((const uint32_t *)d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, n_total, d_bounds, world, da, pa);
         BFQ_CUDA(cudaGetLastError());
     }
     int bits = 1;
-    while (((uint64_t)1 << bits) < n_total) bits++;
-    const int flip = radix_sort_pairs32_16(c, d_keys, kb, d_vals, vb, n, bits);
-    if (flip) {
-        BFQ_CUDA(cudaMemcpyAsync(d_keys, kb, n * 4, cudaMemcpyDeviceToDevice, st));
-        BFQ_CUDA(cudaMemcpyAsync(d_vals, vb, n * 2, cudaMemcpyDeviceToDevice, st));
+    while ((1 << bits) < world) bits++;
+    const int flip = world > 1 ? radix_sort_pairs64(c, da, db, pa, pb, n, bits) : 0;
+    {
+        ProfScope ps(c, PC_ASSEMBLE, n * (8 + 6), 2);
+        split_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(flip ? pb : pa, (uint32_t)n, d_keys, d_vals);
+        dest_counts_kernel<<<1, 256, 0, st>>>(flip ? db : da, (uint32_t)n, world, d_lower);
+        BFQ_CUDA(cudaGetLastError());
     }
-    BFQ_CUDA(cudaMemcpyAsync(d_bounds, text_bounds, (world + 1) * 8, cudaMemcpyHostToDevice, st));
-    bound_counts_kernel<<<1, 256, 0, st>>>(d_keys, (uint32_t)n, d_bounds, world, d_lower);
-    BFQ_CUDA(cudaGetLastError());
     std::vector<uint64_t> lower(world + 1);
     BFQ_CUDA(cudaMemcpyAsync(lower.data(), d_lower, (world + 1) * 8, cudaMemcpyDeviceToHost, st));
     BFQ_CUDA(cudaStreamSynchronize(st));
@@ -271,10 +306,6 @@ void place_pairs_dev(bfq_ctx *c, uint32_t *d_keys, uint16_t *d_vals, uint64_t cn
     Arena::Mark mk = c->arena.mark();
     uint32_t *kb = arena_alloc<uint32_t>(c, cnt + 16);
     uint16_t *vb = arena_alloc<uint16_t>(c, cnt + 16);
-    if (t_lo) {
-        rebase_keys_kernel<<<div_up(cnt, 256), 256, 0, st>>>(d_keys, cnt, (uint32_t)t_lo);
-        BFQ_CUDA(cudaGetLastError());
-    }
     const int flip = radix_sort_permutation(c, d_keys, kb, d_vals, vb, cnt);
     {
         const uint64_t nreads = read_hi - read_lo;

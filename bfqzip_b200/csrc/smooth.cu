@@ -586,7 +586,7 @@ cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
 template <bool FLAT>
 __global__ void __launch_bounds__(256)
 rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8_t *__restrict__ obase,
-              SmoothLists L, const uint8_t *__restrict__ bwt, const uint32_t *__restrict__ SA,
+              SmoothLists L, const uint8_t *__restrict__ bwt, const void *__restrict__ SA, int sa_wide,
               const uint64_t *__restrict__ T3)
 {
     __shared__ uint32_t s_stats[ST_COUNT];
@@ -601,7 +601,10 @@ rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8
         return hdr_code(h, (uint32_t)(i & 31));
     };
     auto prec_code = [&](uint64_t i, uint32_t c) -> uint32_t {      // symbol before row i's symbol c in its read
-        if (FLAT) { const uint32_t p = SA[i]; return p >= 2 ? sym_code(T3, (uint64_t)p - 2) : 0u; }
+        if (FLAT) {
+            const uint64_t p = sa_wide ? ((const uint64_t *)SA)[i] : (uint64_t)((const uint32_t *)SA)[i];
+            return p >= 2 ? sym_code(T3, p - 2) : 0u;
+        }
         LineHdr h = load_hdr(lines, i);
         const uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
         LineHdr h2 = load_hdr(lines, r);
@@ -682,7 +685,7 @@ static void launch_check(bfq_ctx *c) { BFQ_CUDA(cudaGetLastError()); (void)c; }
 
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
                 uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
-                const uint32_t *d_sa, const uint64_t *d_t3, const uint64_t *alpha_hist)
+                const void *d_sa, const uint64_t *d_t3, const uint64_t *alpha_hist, bool sa_wide)
 {
     const bool flat = d_sa != nullptr && d_t3 != nullptr;
     out->flat = flat;
@@ -770,8 +773,8 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     }
     {
         ProfScope ps(c, PC_RULE11, 0);
-        if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, d_t3);
-        else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, d_t3);
+        if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, sa_wide ? 1 : 0, d_t3);
+        else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, 0, d_t3);
         launch_check(c);
     }
     fetch_small(c, c->h_small, d_stats, (ST_COUNT + 2) * 8);

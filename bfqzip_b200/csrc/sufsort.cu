@@ -133,8 +133,9 @@ constexpr int GT_S = GT_T + GT_E;
 constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
 constexpr int GT_GMAX = GT_S / 2;
 
-struct GroupTileArgs {
-    const uint32_t *pos;        // list payload: text position
+template <typename P>
+struct GroupTileArgsT {
+    const P *pos;               // list payload: text position (u32, or u64 for collections of 2^32 rows and more)
     uint32_t m;                 // list length
     int level0;                 // 1: slot == list index, key has no group id
     int ksym;                   // symbols in this level's key (low 3*ksym bits)
@@ -144,7 +145,7 @@ struct GroupTileArgs {
     const uint16_t *QL;         // per text position p: quality of p-1 | (symbols from p to its terminator) << 8
     const uint32_t *g_slot;     // level >= 1: SA slot of the first member of list group g
     const uint32_t *g_off;      // level >= 1: list offset of the first member of list group g
-    uint32_t *SA;               // optional
+    P *SA;                      // optional
     uint8_t *bwt, *qs, *lcp;    // optional (all three or none)
     uint64_t code2byte;
     uint8_t eos;
@@ -158,6 +159,7 @@ struct GroupTileArgs {
     int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
 };
+using GroupTileArgs = GroupTileArgsT<uint32_t>;
 
 __device__ __forceinline__ uint64_t cut_at_terminator(uint64_t w, bool &terminated)
 {
@@ -193,7 +195,8 @@ __device__ __forceinline__ uint32_t head_lcp(K kprev, K kcur, int ksym)
 // data: most members are prefixes of the longest one and a single iteration resolves the group.
 struct RefCmp { uint32_t l, c, r; };
 
-__device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, const uint32_t *s_pos, const uint8_t *s_len,
+template <typename P>
+__device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, const P *s_pos, const uint8_t *s_len,
                                               int depth, uint32_t mem, uint32_t ref, uint32_t D)
 {
     // The strings are read straight from the packed text (L1 / pinned L2): a member is compared once per
@@ -229,9 +232,9 @@ __device__ __forceinline__ uint32_t class_l(uint32_t cls)
 }
 
 // groups of at most 32 * R rows: one row per (slot, lane), keys in registers, shuffles only
-template <int R>
+template <int R, typename P>
 __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
-                                                 const uint32_t *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
+                                                 const P *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
                                                  uint8_t *s_lcpout)
 {
     constexpr uint32_t IB = 6, IM = 63u;                  // position index bits
@@ -347,8 +350,9 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
 }
 
 // groups of any size that fits the window: keys in shared memory, lanes stride over the rows
+template <typename P>
 __device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
-                                                 const uint32_t *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
+                                                 const P *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
                                                  uint8_t *s_lcpout, uint64_t *s_key, uint16_t *s_runa, uint8_t *s_rdepth)
 {
     uint32_t n2 = 2;
@@ -434,14 +438,14 @@ __device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int 
     for (uint32_t t = lane; t < len; t += 32) s_sorted[gs + t] = (uint16_t)(gs + (uint32_t)(key[t] & 0x7FFu));
 }
 
-template <typename K>
+template <typename K, typename P>
 __global__ void __launch_bounds__(GT_THREADS)
-group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
+group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
     uint64_t *s_key = reinterpret_cast<uint64_t *>(gt_smem);                        // [GT_S] keys of groups > 64 rows
-    uint32_t *s_pos = reinterpret_cast<uint32_t *>(s_key + GT_S);                   // [GT_S] text position of the row's suffix
-    uint32_t *s_best = s_pos + GT_S;                                                // [GT_S] (length << 16 | row) of a run's reference
+    P *s_pos = reinterpret_cast<P *>(s_key + GT_S);                                 // [GT_S] text position of the row's suffix
+    uint32_t *s_best = reinterpret_cast<uint32_t *>(s_pos + GT_S);                                                // [GT_S] (length << 16 | row) of a run's reference
     uint32_t *s_head = s_best + GT_S;                                               // [GT_HW]
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] previous symbol code | its quality << 8
     uint16_t *s_gs = s_prev + GT_S;                                                 // [GT_S] group start or 0xFFFF (row not owned)
@@ -531,7 +535,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
                 }
                 if (fits) {
                     gs16 = (uint16_t)gs;
-                    const uint32_t p = __ldcs(&A.pos[j]);
+                    const P p = __ldcs(&A.pos[j]);
                     s_sorted[r] = (uint16_t)r;
                     const uint32_t ql = A.embed ? (uint32_t)((uint64_t)keys[j] >> 48) : (uint32_t)A.QL[p];
                     if (A.bwt) {
@@ -555,9 +559,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
         const uint32_t gs = s_gstart[g], len = s_glen[g];
-        if (len <= 32) order_group_regs<1>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
-        else if (len <= 64) order_group_regs<2>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
-        else order_group_smem(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
+        if (len <= 32) order_group_regs<1, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
+        else if (len <= 64) order_group_regs<2, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
+        else order_group_smem<P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
         __syncwarp();
     }
     __syncthreads();
@@ -580,9 +584,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgs A)
     }
 }
 
-static size_t group_tile_smem(int)
+static size_t group_tile_smem(size_t pos_bytes)
 {
-    return (size_t)GT_S * 8 + (size_t)GT_S * 4 * 2 + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
+    return (size_t)GT_S * 8 + (size_t)GT_S * (4 + pos_bytes) + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
            (size_t)GT_S * 3 + 16;
 }
 
@@ -653,16 +657,17 @@ scan_excl_u32_kernel(const uint32_t *__restrict__ in, uint32_t *__restrict__ out
 }
 
 // next-level list: members of deferred group d get key (d << 3s) | next s symbols
+template <typename P>
 __global__ void __launch_bounds__(256)
-defer_fill_kernel(const uint32_t *__restrict__ pos, const uint32_t *__restrict__ dstart,
+defer_fill_kernel(const P *__restrict__ pos, const uint32_t *__restrict__ dstart,
                   const uint32_t *__restrict__ dlen, const uint32_t *__restrict__ doff, uint32_t G,
                   const uint64_t *__restrict__ T3, int depth, int s, uint64_t *__restrict__ keys_out,
-                  uint32_t *__restrict__ pos_out)
+                  P *__restrict__ pos_out)
 {
     for (uint32_t d = blockIdx.x; d < G; d += gridDim.x) {
         const uint32_t start = dstart[d], len = dlen[d], off = doff[d];
         for (uint32_t i = threadIdx.x; i < len; i += 256) {
-            const uint32_t p = pos[start + i];
+            const P p = pos[start + i];
             keys_out[off + i] = ((uint64_t)d << (3 * s)) | cut_key(T3, (uint64_t)p + depth, s);
             pos_out[off + i] = p;
         }
@@ -692,23 +697,23 @@ Alphabet alphabet_from_hist(const uint64_t hist[256], uint8_t eos, bool eos_may_
     return A;
 }
 
-template <typename K>
-static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgs &A)
+template <typename K, typename P>
+static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgsT<P> &A)
 {
-    const size_t smem = group_tile_smem(A.W);
-    BFQ_CUDA(cudaFuncSetAttribute(group_tile_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = group_tile_smem(sizeof(P));
+    BFQ_CUDA(cudaFuncSetAttribute(group_tile_kernel<K, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const uint32_t ntiles = div_up(A.m, GT_T);
     bfq_ctx::HostSink *sink = c->sink;
     // host-buffer call: the finished rows leave for the host slice by slice while the next slice is ordered
     const uint32_t nslices = (sink && A.level0 && A.bwt && (sink->bwt || sink->qs || sink->lcp) && ntiles >= 4096) ? (uint32_t)c->opt_host_slices : 1;
     const uint32_t per = div_up(ntiles, nslices);
     for (uint32_t s = 0; s < nslices; s++) {
-        GroupTileArgs B = A;
+        GroupTileArgsT<P> B = A;
         B.tile0 = s * per;
         const uint32_t cnt = std::min(per, ntiles - B.tile0);
         {
             ProfScope ps(c, PC_GROUP, (uint64_t)cnt * GT_T * (sizeof(K) + 4 + 3 + 4 * (uint64_t)A.W));
-            group_tile_kernel<K><<<cnt, GT_THREADS, smem, c->stream>>>(keys, B);
+            group_tile_kernel<K, P><<<cnt, GT_THREADS, smem, c->stream>>>(keys, B);
             BFQ_CUDA(cudaGetLastError());
         }
         if (nslices > 1) {
@@ -726,13 +731,18 @@ static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgs &A)
 
 size_t packed_text_words(uint64_t N) { return ((N + 320 + 63) / 64) * 3 + 2; }
 
-void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
-                    uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
-                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep, KeyRange *range)
+// P = type of a text position: u32, or u64 for a collection of 2^32 rows and more (only as a key range: the rows of ONE
+// GPU are always indexed with 32 bits)
+template <typename P>
+static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                            uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
+                            uint8_t *d_qs, uint8_t *d_lcp, P *d_sa_out, uint64_t *d_t3_keep, KeyRange *range)
 {
     const uint64_t N = total_bases + nreads;
     if (N == 0) return;
-    if (N >= ((uint64_t)1 << 32) - 64) BFQ_FAIL(BFQ_ETOOLARGE, "collection has %llu rows; this build indexes rows with 32 bits", (unsigned long long)N);
+    if (sizeof(P) == 4 && N >= ((uint64_t)1 << 32) - 64)
+        BFQ_FAIL(BFQ_ETOOLARGE, "collection has %llu rows; this build indexes rows with 32 bits", (unsigned long long)N);
+    if (sizeof(P) == 8 && !range) BFQ_FAIL(BFQ_ETOOLARGE, "64-bit text positions are only built for key ranges (single-collection mode)");
     if (max_len > 255)
         BFQ_FAIL(BFQ_EINVAL, "a read has %llu symbols; reads are limited to 255 (1-byte LCP entries, dataTypelenSeq is uchar, parameters.h:68)",
                  (unsigned long long)max_len);
@@ -757,7 +767,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     // a key range sorts about N / world suffixes; keyB also hosts the byte text (N + 1 bytes) while packing
     const uint64_t cap = range ? std::max<uint64_t>(range->capacity, N / 8 + 64) : N;
     uint64_t *keyA = arena_alloc<uint64_t>(c, cap), *keyB = arena_alloc<uint64_t>(c, cap);
-    uint32_t *posA = arena_alloc<uint32_t>(c, cap), *posB = arena_alloc<uint32_t>(c, cap);
+    P *posA = arena_alloc<P>(c, cap), *posB = arena_alloc<P>(c, cap);
     const uint32_t dcap = (uint32_t)(N / std::min<uint64_t>(GT_E, (uint64_t)c->opt_group_cap + 1) + 64);
     uint32_t *dtab[2][4];                                   // per level parity: start, len, slot, off
     for (int a = 0; a < 2; a++)
@@ -783,14 +793,16 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     uint64_t n_sort = N, prev_key = 0;
     bool has_prev = false;
     if (range) {
-        flip = radix_sort_suffix_keys_range(c, T3, k <= 16 ? QL : nullptr, N, k, range->rank, range->world, keyA, keyB, posA, posB,
-                                            range->capacity, &range->n_local, &range->row_base, &prev_key, &has_prev);
+        flip = radix_sort_suffix_keys_range<P>(c, T3, k <= 16 ? QL : nullptr, N, k, range->rank, range->world, keyA, keyB, posA, posB,
+                                               range->capacity, &range->n_local, &range->row_base, &prev_key, &has_prev);
         n_sort = range->n_local;
         if (n_sort == 0) return;
-    } else
+    } else if constexpr (sizeof(P) == 4)
         flip = radix_sort_suffix_keys(c, T3, k <= 16 ? QL : nullptr, N, k, keyA, keyB, posA, posB);
+    else
+        flip = 0;
     uint64_t *keys = flip ? keyB : keyA, *keys_alt = flip ? keyA : keyB;
-    uint32_t *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
+    P *pos = flip ? posB : posA, *pos_alt = flip ? posA : posB;
 
     c->trace("suffix keys sorted", st);
     // The packed text is what every group gathers from at random: pin it in L2 (persisting access
@@ -822,7 +834,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
     } unpin{st, pinned};
 
     auto words_for = [&](int depth) { return (int)std::max<int64_t>(0, ((int64_t)max_len - depth + 20) / 21); };
-    GroupTileArgs G;
+    GroupTileArgsT<P> G;
     memset(&G, 0, sizeof G);
     G.T3 = T3; G.QL = QL; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
@@ -840,7 +852,7 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         G.g_slot = level ? dtab[parity ^ 1][2] : nullptr;
         G.g_off = level ? dtab[parity ^ 1][3] : nullptr;
         G.defer_start = dtab[parity][0];
-        launch_group_tile<uint64_t>(c, keys, G);
+        launch_group_tile<uint64_t, P>(c, keys, G);
         fetch_small(c, c->h_small, dcount, 4);
         BFQ_CUDA(cudaStreamSynchronize(st));
         const uint32_t ndef = ((uint32_t *)c->h_small)[0];
@@ -866,15 +878,29 @@ void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, 
         {
             ProfScope ps(c, PC_DEFER, (uint64_t)m2 * (4 + 12 + 16));
             int grid = (int)std::min<uint64_t>(ndef, (uint64_t)c->num_sms * 8);
-            defer_fill_kernel<<<grid, 256, 0, st>>>(pos, dstart, dlen, doff, ndef, T3, depth, s, keys_alt, pos_alt);
+            defer_fill_kernel<P><<<grid, 256, 0, st>>>(pos, dstart, dlen, doff, ndef, T3, depth, s, keys_alt, pos_alt);
             BFQ_CUDA(cudaGetLastError());
         }
-        flip = radix_sort_pairs64(c, keys_alt, keys, pos_alt, pos, m2, gbits + 3 * s);
+        flip = radix_sort_pairs64(c, keys_alt, keys, pos_alt, pos, m2, gbits + 3 * s);     // overloaded on the payload type
         if (!flip) { std::swap(keys, keys_alt); std::swap(pos, pos_alt); }
         m = m2;
         ksym = s;
         parity ^= 1;
     }
+}
+
+void build_ebwt_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                    uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
+                    uint8_t *d_qs, uint8_t *d_lcp, uint32_t *d_sa_out, uint64_t *d_t3_keep, KeyRange *range)
+{
+    build_ebwt_impl<uint32_t>(c, d_bases, d_quals, d_off, nreads, total_bases, max_len, eos, d_bwt, d_qs, d_lcp, d_sa_out, d_t3_keep, range);
+}
+
+void build_ebwt_dev_wide(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
+                         uint64_t nreads, uint64_t total_bases, uint64_t max_len, uint8_t eos, uint8_t *d_bwt,
+                         uint8_t *d_qs, uint8_t *d_lcp, uint64_t *d_sa_out, uint64_t *d_t3_keep, KeyRange *range)
+{
+    build_ebwt_impl<uint64_t>(c, d_bases, d_quals, d_off, nreads, total_bases, max_len, eos, d_bwt, d_qs, d_lcp, d_sa_out, d_t3_keep, range);
 }
 
 } // namespace bfq

@@ -75,6 +75,8 @@ class OracleEngine:
         o = np.argsort(k, kind="stable")
         k, v = k[o], v[o]
         counts = np.array([np.count_nonzero((k >= int(tb[d])) & (k < int(tb[d + 1]))) for d in range(world)], np.uint64)
+        dest = np.searchsorted(tb.astype(np.int64), k, side="right") - 1
+        k = k - tb.astype(np.int64)[dest]                    # positions travel relative to the destination's first one
         stats = {kk: (vv if rank == 0 else 0) for kk, vv in st.items()}        # the counters are summed over ranks
         return dict(n_local=b - a, row_base=a, bwt=bwt[a:b], qs=qs[a:b], lcp=lcp[a:b],
                     keys=torch.from_numpy(k.astype(np.int32)), vals=torch.from_numpy(v.astype(np.int16)), counts=counts, stats=stats)
@@ -82,7 +84,7 @@ class OracleEngine:
     def place(self, keys, vals, count, text_lo, dreads, read_lo, read_hi, nbases):
         import torch
         off = dreads[2]
-        k = keys[:count].numpy().astype(np.int64) - text_lo
+        k = keys[:count].numpy().astype(np.int64)
         v = vals[:count].numpy().astype(np.int64) & 0xFFFF
         assert np.array_equal(np.sort(k), np.arange(count))
         t = np.empty(count, np.int64); t[k] = v

@@ -33,6 +33,13 @@ def test_dist_matches_oracle(world):
     check(synth.make_reads(20000, 100, 900 + world), 2, 0, world)
 
 
+@pytest.mark.parametrize("world", [1, 2, 5])
+def test_dist_wide_positions(world):
+    """64-bit text positions (what collections of 2^32 rows and more use), forced on a small collection."""
+    check(synth.make_reads(15000, 100, 31 + world), 2, 0, world, options={"wide_positions": 1})
+    check(synth.make_reads(4000, 70, 32 + world), 0, 1, world, options={"wide_positions": 1, "group_cap": 8})
+
+
 @pytest.mark.parametrize("mode", [(0, 1), (1, 0), (3, 1)], ids=lambda m: f"M{m[0]}B{m[1]}")
 def test_dist_modes(mode):
     check(synth.make_reads(12000, 80, 77), mode[0], mode[1], 3)
