@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--B", type=int, default=0)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--nocheck", action="store_true")
+    ap.add_argument("--torchgen", action="store_true", help="generate the reads on the GPU (large collections); size-independent checks only")
+    ap.add_argument("--opt", action="append", default=[], help="ctx option key=value")
     a = ap.parse_args()
     import torch
     import torch.distributed as td
@@ -33,14 +35,49 @@ def main():
     torch.cuda.set_device(lr)
     if world > 1:
         td.init_process_group("nccl", device_id=torch.device("cuda", lr))
-    reads = synth.make_reads(a.nreads, a.len, 1001)
-    bases, quals, off = reads
     P = lib.default_params(eos=0)
-    eng = dist.GpuEngine(a.M, a.B, lr)
-    dreads = eng.upload(reads)
+    eng = dist.GpuEngine(a.M, a.B, lr, dict(kv.split("=") for kv in a.opt))
+    if a.torchgen:
+        from prof_step import torch_reads
+        d_b, d_q, off = torch_reads(torch, torch.device("cuda", lr), a.nreads, a.len, 1001)
+        reads = (None, None, off)
+        torch.cuda.empty_cache()          # the library allocates outside torch's cache
+        dreads = (d_b, d_q, torch.from_numpy(off.view(np.int64)).to(d_b.device))
+    else:
+        reads = synth.make_reads(a.nreads, a.len, 1001)
+        dreads = eng.upload(reads)
+    bases, quals, off = reads
     sl, (ob, oq), (lo, hi), st = dist.run_single_collection(eng, reads, P, rank, world, dreads=dreads)
     ok = True
-    if not a.nocheck:
+    props = None
+    if a.torchgen and not a.nocheck:
+        # size-independent properties, summed over the ranks: the slices tile the row range, the eBWT and QS slices are
+        # together a permutation of the text, LCP <= read length, bases differ from the input exactly `modified` times,
+        # qualities change only to the smoothing value (mode M=2; the other modes compute the new quality per cluster)
+        d_b, d_q, d_off = dreads
+        N = int(off[-1]) + len(off) - 1
+        s, e = int(off[lo]), int(off[hi])
+        hb = torch.bincount(sl["bwt"].long(), minlength=256); hq = torch.bincount(sl["qs"].long(), minlength=256)
+        nd = (ob != d_b[s:e]).sum(); ch = oq != d_q[s:e]
+        badq = (ch & (oq != ord(">"))).sum()
+        v = torch.cat([hb, hq, torch.stack([nd, badq, sl["lcp"].max().long() if sl["n_local"] else nd * 0,
+                                            torch.tensor(sl["n_local"], device=nd.device)])]).to(torch.int64)
+        rows = torch.tensor([sl["row_base"], sl["n_local"]], device=v.device, dtype=torch.int64)
+        if world > 1:
+            mx = v[514:515].clone(); td.all_reduce(mx, op=td.ReduceOp.MAX)
+            td.all_reduce(v)
+            rl = [torch.empty_like(rows) for _ in range(world)]; td.all_gather(rl, rows)
+        else:
+            mx = v[514:515]; rl = [rows]
+        want_b = torch.bincount(d_b.long(), minlength=256); want_b[0] += len(off) - 1
+        want_q = torch.bincount(d_q.long(), minlength=256); want_q[0] += len(off) - 1
+        spans = sorted((int(x[0]), int(x[1])) for x in rl)
+        tiles = spans[0][0] == 0 and all(a0 + n0 == b0 for (a0, n0), (b0, _) in zip(spans, spans[1:])) and spans[-1][0] + spans[-1][1] == N
+        props = {"rows_tile": tiles, "bwt_is_permutation": bool(torch.equal(v[:256], want_b)), "qs_is_permutation": bool(torch.equal(v[256:512], want_q)),
+                 "bases_changed": int(v[512]), "stats_modified": st["modified"], "bad_quality_changes": int(v[513]), "max_lcp": int(mx[0]), "rows": N}
+        ok = tiles and props["bwt_is_permutation"] and props["qs_is_permutation"] and props["bases_changed"] == st["modified"] \
+            and (props["bad_quality_changes"] == 0 or a.M != 2) and props["max_lcp"] <= a.len
+    elif not a.nocheck:
         g = lib.BfqGpu(a.M, a.B, lr)
         (bwt, qs, lcp), (fb, fq), fst = g.pipeline(bases, quals, off, P)
         g.close()
@@ -72,7 +109,8 @@ def main():
         print(json.dumps({"mode": "single_collection", "n_gpus": world, "nreads": a.nreads, "len": a.len, "ms_per_step_best": ms,
                           "ms_all": [round(x, 3) for x in times], "gbases_s": int(off[-1]) / ms / 1e6,
                           "slice_rows": [int(x[2]) for x in tl], "parity_ok_all_ranks": all(float(x[1]) == 1.0 for x in tl),
-                          "checked": not a.nocheck}), flush=True)
+                          "checked": not a.nocheck, "props": props, "stats": st,
+                          "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 1)}), flush=True)
     eng.close()
     if world > 1:
         td.destroy_process_group()

@@ -15,6 +15,33 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 
+def torch_reads(torch, dev, nreads, L, seed):
+    """synth.make_reads' model (40x coverage, SNP haplotype, 1 % errors, an N every 1000th read) generated on the device."""
+    gen = torch.Generator(device=dev); gen.manual_seed(seed)
+    glen = max(L + 1, nreads * L // 40)
+    hap = torch.randint(0, 4, (2, glen), device=dev, dtype=torch.uint8, generator=gen)
+    hap[1] = hap[0]
+    snp = torch.arange(500, glen, 1000, device=dev)
+    hap[1, snp] = (hap[0, snp] + torch.randint(1, 4, snp.shape, device=dev, dtype=torch.uint8, generator=gen)) & 3
+    start = torch.randint(0, glen - L + 1, (nreads,), device=dev, generator=gen)
+    which = torch.randint(0, 2, (nreads,), device=dev, generator=gen)
+    acgt = torch.tensor(list(b"ACGT"), device=dev, dtype=torch.uint8)
+    d_b = torch.empty((nreads, L), device=dev, dtype=torch.uint8); d_q = torch.empty_like(d_b)
+    CH = 1 << 20
+    for s0 in range(0, nreads, CH):
+        s1 = min(nreads, s0 + CH)
+        idx = start[s0:s1, None] + torch.arange(L, device=dev)[None, :]
+        codes = hap.reshape(-1)[which[s0:s1, None] * glen + idx]
+        err = torch.rand(codes.shape, device=dev, generator=gen) < 0.01
+        codes = torch.where(err, (codes + torch.randint(1, 4, codes.shape, device=dev, dtype=torch.uint8, generator=gen)) & 3, codes)
+        qq = torch.randint(25, 42, codes.shape, device=dev, dtype=torch.uint8, generator=gen)
+        qq = torch.where(err, torch.randint(2, 16, codes.shape, device=dev, dtype=torch.uint8, generator=gen), qq) + 33
+        d_b[s0:s1] = acgt[codes.long()]; d_q[s0:s1] = qq
+    d_b[::1000, 7] = ord("N"); d_q[::1000, 7] = ord("#")
+    off = np.arange(nreads + 1, dtype=np.uint64) * np.uint64(L)
+    return d_b.reshape(-1), d_q.reshape(-1), off
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--nreads", type=int, default=1_000_000)
@@ -32,33 +59,8 @@ def main():
     from bfqzip_b200 import lib, synth
     dev = torch.device("cuda", 0)
     if a.torchgen:
-        # same model as synth.make_reads (40x coverage, SNP haplotype, 1 % errors, an N every 1000th read), on the device
-        gen = torch.Generator(device=dev); gen.manual_seed(a.seed)
-        nreads, L = a.nreads, a.len
-        glen = max(L + 1, nreads * L // 40)
-        hap = torch.randint(0, 4, (2, glen), device=dev, dtype=torch.uint8, generator=gen)
-        hap[1] = hap[0]
-        snp = torch.arange(500, glen, 1000, device=dev)
-        hap[1, snp] = (hap[0, snp] + torch.randint(1, 4, snp.shape, device=dev, dtype=torch.uint8, generator=gen)) & 3
-        start = torch.randint(0, glen - L + 1, (nreads,), device=dev, generator=gen)
-        which = torch.randint(0, 2, (nreads,), device=dev, generator=gen)
-        acgt = torch.tensor(list(b"ACGT"), device=dev, dtype=torch.uint8)
-        d_b = torch.empty((nreads, L), device=dev, dtype=torch.uint8); d_q = torch.empty_like(d_b)
-        CH = 1 << 20
-        for s0 in range(0, nreads, CH):
-            s1 = min(nreads, s0 + CH)
-            idx = start[s0:s1, None] + torch.arange(L, device=dev)[None, :]
-            codes = hap.reshape(-1)[which[s0:s1, None] * glen + idx]
-            err = torch.rand(codes.shape, device=dev, generator=gen) < 0.01
-            codes = torch.where(err, (codes + torch.randint(1, 4, codes.shape, device=dev, dtype=torch.uint8, generator=gen)) & 3, codes)
-            qq = torch.randint(25, 42, codes.shape, device=dev, dtype=torch.uint8, generator=gen)
-            qq = torch.where(err, torch.randint(2, 16, codes.shape, device=dev, dtype=torch.uint8, generator=gen), qq) + 33
-            d_b[s0:s1] = acgt[codes.long()]; d_q[s0:s1] = qq
-        d_b[::1000, 7] = ord("N"); d_q[::1000, 7] = ord("#")
-        d_b = d_b.reshape(-1); d_q = d_q.reshape(-1)
-        off = np.arange(nreads + 1, dtype=np.uint64) * np.uint64(L)
+        d_b, d_q, off = torch_reads(torch, dev, a.nreads, a.len, a.seed)
         bases = quals = None
-        del hap, start, which
     else:
         bases, quals, off = synth.make_reads(a.nreads, a.len, a.seed)
     nreads = len(off) - 1
