@@ -13,6 +13,9 @@
 #include <getopt.h>
 #include <iostream>
 #include <chrono>
+#include <future>
+#include <tuple>
+#include <string>
 #include <memory>
 #include <algorithm>
 
@@ -103,18 +106,27 @@ int main(int argc, char **argv)
 
     try {
         auto t0 = std::chrono::steady_clock::now();
+        // the CUDA context comes up (seconds on a cold GPU) while the inputs are mapped and counted
+        auto ctx_ready = std::async(std::launch::async, [device] {
+            bfq_ctx *x = nullptr;
+            int rc = bfq_ctx_create(&x, device);
+            return std::make_tuple(rc, x, std::string(rc == BFQ_OK ? "" : bfq_last_error()));     // the message is thread-local
+        });
         bfqio::MappedFile fb(input_dna), fq(input_qual), fl(input_lcp);
         const uint64_t n = fb.size;
         if (fq.size != n || fl.size != n) {
             std::cerr << "Error: " << input_dna << ", " << input_qual << " and " << input_lcp << " must have the same length (1-byte LCP entries)" << endl;
+            bfq_ctx_destroy(std::get<1>(ctx_ready.get()));
             return EXIT_FAILURE;
         }
         uint64_t nreads = 0;
         for (uint64_t i = 0; i < n; i++) nreads += fb.data[i] == P.eos_byte;     // numSeq (bfq_ext.cpp:160-166)
         std::vector<uint8_t> ob(n ? n : 1), oq(n ? n : 1);
         std::vector<uint64_t> off(nreads + 1);
-        bfq_ctx *ctx = nullptr;
-        if (bfq_ctx_create(&ctx, device) != BFQ_OK) { std::cerr << "Error: " << bfq_last_error() << endl; return EXIT_FAILURE; }
+        auto tp = std::chrono::steady_clock::now();
+        auto cr = ctx_ready.get();
+        bfq_ctx *ctx = std::get<1>(cr);
+        if (std::get<0>(cr) != BFQ_OK) { std::cerr << "Error: " << std::get<2>(cr) << endl; return EXIT_FAILURE; }
         bfq_stats S;
         auto t1 = std::chrono::steady_clock::now();
         int rc = bfq_smooth_rebuild(ctx, fb.data, fq.data, fl.data, n, &P, ob.data(), oq.data(), off.data(), nreads + 1, &S);
@@ -160,7 +172,7 @@ int main(int argc, char **argv)
              << 100 * double(S.modified) / S.bases_inside << "% of bases inside clusters)." << endl;
         cout << "***********************" << endl << endl;
         auto sec = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
-        cout << "GPU timing: load " << sec(t0, t1) << " s, smooth+rebuild " << sec(t1, t2) << " s, write " << sec(t2, t3) << " s" << endl;
+        cout << "GPU timing: load " << sec(t0, t1) << " s (inputs " << sec(t0, tp) << " s), smooth+rebuild " << sec(t1, t2) << " s, write " << sec(t2, t3) << " s" << endl;
     } catch (std::exception &e) {
         std::cerr << "Error: " << e.what() << endl;
         return EXIT_FAILURE;
