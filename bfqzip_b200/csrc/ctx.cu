@@ -18,6 +18,7 @@ void fetch_small(bfq_ctx *c, void *host_dst, const void *dev_src, size_t bytes)
     }
     uint32_t *dst = (uint32_t *)((char *)c->h_small_dev + ((char *)host_dst - (char *)c->h_small));
     fetch_small_kernel<<<1, 256, 0, c->stream>>>(dst, (const uint32_t *)dev_src, (uint32_t)(bytes / 4));
+    c->launches++;
     BFQ_CUDA(cudaGetLastError());
 }
 

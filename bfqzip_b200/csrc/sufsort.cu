@@ -94,18 +94,37 @@ pack3_kernel(const uint8_t *__restrict__ T8, uint64_t n, uint64_t ngroups, uint6
 {
     const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= ngroups) return;
-    uint64_t w[4] = {0, 0, 0, 0};
     const uint64_t base = g * 64;
-#pragma unroll 8
-    for (int j = 0; j < 64; j++) {
-        uint64_t code = (base + j < n) ? (uint64_t)T8[base + j] : 0ull;
-        int bit = 3 * j, wi = bit >> 6, sh = 61 - (bit & 63);
-        if (sh >= 0) w[wi] |= code << sh;
-        else { w[wi] |= code >> (-sh); w[wi + 1] |= code << (64 + sh); }
+    // 8 codes (one 64-bit load, first code in the low byte) -> 24 bits, first code in the top 3 bits
+    auto pack8 = [](uint64_t x) -> uint64_t {
+        uint64_t r = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) r |= ((x >> (8 * j)) & 7ull) << (21 - 3 * j);
+        return r;
+    };
+    uint64_t f[8];                                        // 8 fields of 24 bits = 192 bits
+    if (base + 64 <= n) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(T8 + base);      // T8 is 256-byte aligned, base a multiple of 64
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 v = __ldcs(src + q);
+            f[2 * q] = pack8((uint64_t)v.x | ((uint64_t)v.y << 32));
+            f[2 * q + 1] = pack8((uint64_t)v.z | ((uint64_t)v.w << 32));
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < 8; q++) {
+            uint64_t x = 0;
+            for (int j = 0; j < 8; j++) {
+                const uint64_t i = base + 8 * q + j;
+                if (i < n) x |= (uint64_t)T8[i] << (8 * j);
+            }
+            f[q] = pack8(x);
+        }
     }
-    T3[g * 3 + 0] = w[0];
-    T3[g * 3 + 1] = w[1];
-    T3[g * 3 + 2] = w[2];
+    T3[g * 3 + 0] = (f[0] << 40) | (f[1] << 16) | (f[2] >> 8);
+    T3[g * 3 + 1] = (f[2] << 56) | (f[3] << 32) | (f[4] << 8) | (f[5] >> 16);
+    T3[g * 3 + 2] = (f[5] << 48) | (f[6] << 24) | f[7];
 }
 
 
