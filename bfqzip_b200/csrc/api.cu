@@ -73,11 +73,8 @@ export_rows_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict_
         ob_out[i] = (q & 0x80) ? obase[i] : flat_bwt[i];
         return;
     }
-    const uint8_t *L = lines + (i >> 5) * 64;
-    const uint32_t *H = reinterpret_cast<const uint32_t *>(L);
-    const uint32_t r = (uint32_t)(i & 31);
-    const uint32_t c = ((H[5] >> r) & 1u) | (((H[6] >> r) & 1u) << 1) | (((H[7] >> r) & 1u) << 2);
-    const uint8_t q = L[32 + r];
+    const uint32_t c = ws_code(ws_load(lines, i), (uint32_t)(i & 15));
+    const uint8_t q = *ws_q(lines, i);
     qs_out[i] = q & 0x7F;
     ob_out[i] = (q & 0x80) ? obase[i] : (uint8_t)(code2byte >> (8 * c));
 }

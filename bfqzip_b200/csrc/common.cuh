@@ -69,6 +69,35 @@ struct Arena {
 
 // ---- packed text (3-bit codes, 64 symbols per three u64 words, first symbol in the most significant bits)
 #ifdef __CUDACC__
+// ---- walk sectors: what one inverse-LF step reads.  32 bytes per 16 BWT rows -- ONE DRAM sector per step:
+//   u16 rel[5]   occurrences of code 1..5 in the rows of this super-block before the sector
+//   u16 plane[3] bit-sliced codes of the 16 rows
+//   u8  q[16]    stored quality (bit 7 = "base modified", the base is then in obase[row])
+// plus a table of u32[8] per super-block of 8192 rows (absolute occurrences before the block + pile start; cache resident).
+constexpr int WS_SUPER_SHIFT = 13;
+struct WalkSector { uint32_t rel[5]; uint32_t plane[3]; };
+__device__ __forceinline__ WalkSector ws_load(const uint8_t *__restrict__ lines, uint64_t row)
+{
+    const uint4 a = *reinterpret_cast<const uint4 *>(lines + (row >> 4) * 32);
+    WalkSector s;
+    s.rel[0] = a.x & 0xFFFFu; s.rel[1] = a.x >> 16; s.rel[2] = a.y & 0xFFFFu; s.rel[3] = a.y >> 16; s.rel[4] = a.z & 0xFFFFu;
+    s.plane[0] = a.z >> 16; s.plane[1] = a.w & 0xFFFFu; s.plane[2] = a.w >> 16;
+    return s;
+}
+__device__ __forceinline__ uint32_t ws_code(const WalkSector &s, uint32_t r)          // r = row & 15
+{
+    return ((s.plane[0] >> r) & 1u) | (((s.plane[1] >> r) & 1u) << 1) | (((s.plane[2] >> r) & 1u) << 2);
+}
+__device__ __forceinline__ uint64_t ws_lf(const WalkSector &s, const uint32_t *__restrict__ super, uint64_t row, uint32_t c)   // c in 1..5
+{
+    const uint32_t r = (uint32_t)(row & 15);
+    const uint32_t mm = ((c & 1) ? s.plane[0] : ~s.plane[0]) & ((c & 2) ? s.plane[1] : ~s.plane[1]) &
+                        ((c & 4) ? s.plane[2] : ~s.plane[2]);
+    return (uint64_t)super[(row >> WS_SUPER_SHIFT) * 8 + (c - 1)] + s.rel[c - 1] + __popc(mm & ((1u << r) - 1u));
+}
+__device__ __forceinline__ uint8_t *ws_q(uint8_t *lines, uint64_t row) { return lines + (row >> 4) * 32 + 16 + (row & 15); }
+__device__ __forceinline__ const uint8_t *ws_q(const uint8_t *lines, uint64_t row) { return lines + (row >> 4) * 32 + 16 + (row & 15); }
+
 // 21 symbols starting at text position p, in bits 63..1 (bit 0 cleared)
 __device__ __forceinline__ uint64_t text_window(const uint64_t *__restrict__ T3, uint64_t p)
 {
@@ -223,7 +252,8 @@ void build_ebwt_dev_wide(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
 size_t packed_text_words(uint64_t N);     // u64 words build_ebwt_dev needs for the packed text of N rows
 // smooth.cu
 struct SmoothResult {
-    uint8_t *lines = nullptr;     // 64 B per 32 rows: u32 cnt[5], u32 plane[3], u8 q[32]
+    uint8_t *lines = nullptr;     // walk sectors: 32 B per 16 rows (see ws_load)
+    const uint32_t *super = nullptr;   // u32[8] per 8192 rows: occurrences before the super-block + pile start
     uint8_t *obase = nullptr;     // n bytes, valid where q&0x80
     bool flat = false;            // lines is a plain per-row array of stored qualities (no walk lines were built)
     uint64_t n = 0, nreads = 0;

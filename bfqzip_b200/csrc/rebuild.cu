@@ -18,7 +18,7 @@ struct WalkHdr { uint32_t cnt[5]; uint32_t plane[3]; };
 // final place.  Otherwise they go to a [nreads x max_len] scratch in walk order and lens[g]
 // records how many were found; assemble_kernel reverses and compacts them.
 __global__ void __launch_bounds__(256)
-walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase, uint32_t nreads,
+walk_kernel(const uint8_t *__restrict__ lines, const uint32_t *__restrict__ super, const uint8_t *__restrict__ obase, uint32_t nreads,
             int max_len, uint64_t code2byte, const uint64_t *__restrict__ off_known,
             uint8_t *__restrict__ out_b, uint8_t *__restrict__ out_q, uint32_t *__restrict__ lens, uint32_t g0 = 0)
 {
@@ -36,14 +36,11 @@ walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase
     const bool wide = ((reinterpret_cast<uintptr_t>(out_b) | reinterpret_cast<uintptr_t>(out_q)) & 7) == 0;
     int k = 0;
     for (; k < max_len; k++) {
-        const uint8_t *L = lines + (row >> 5) * 64;
-        const uint4 a = *reinterpret_cast<const uint4 *>(L);
-        const uint4 b = *reinterpret_cast<const uint4 *>(L + 16);
-        const uint32_t r = (uint32_t)(row & 31);
-        const uint32_t p0 = b.y, p1 = b.z, p2 = b.w;
-        const uint32_t c = ((p0 >> r) & 1u) | (((p1 >> r) & 1u) << 1) | (((p2 >> r) & 1u) << 2);
+        // one 32-byte sector per step: codes + in-block counts in its first half, the row's quality in the second
+        const WalkSector S = ws_load(lines, row);
+        const uint8_t q = *ws_q(lines, row);
+        const uint32_t c = ws_code(S, (uint32_t)(row & 15));
         if (c == 0) break;                                   // end-marker: read complete
-        const uint8_t q = L[32 + r];
         uint8_t base = (uint8_t)(code2byte >> (8 * c));
         if (q & 0x80) base = obase[row];                     // noise-reduced row (BWT_MOD, bfq_ext.cpp:555)
         if (off_known) {
@@ -61,9 +58,7 @@ walk_kernel(const uint8_t *__restrict__ lines, const uint8_t *__restrict__ obase
                 cnt = 0;
             }
         } else { out_b[wpos] = base; out_q[wpos] = q & 0x7F; wpos++; }
-        const uint32_t mm = ((c & 1) ? p0 : ~p0) & ((c & 2) ? p1 : ~p1) & ((c & 4) ? p2 : ~p2);
-        const uint32_t cntc = c == 1 ? a.x : c == 2 ? a.y : c == 3 ? a.z : c == 4 ? a.w : b.x;
-        row = (uint64_t)cntc + __popc(mm & ((1u << r) - 1u));
+        row = ws_lf(S, super, row, c);
     }
     if (off_known)
         for (int t = 0; t < cnt; t++) { out_b[wpos + t] = (uint8_t)(accb >> (8 * t)); out_q[wpos + t] = (uint8_t)(accq >> (8 * t)); }
@@ -341,8 +336,8 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P, const u
         for (uint64_t g0 = 0; g0 < R; g0 += step) {
             const uint64_t g1 = std::min(R, g0 + step);
             {
-                ProfScope ps(c, PC_WALK, (S.n - R) * (64 + 2) * (g1 - g0) / R);
-                walk_kernel<<<div_up(g1 - g0, 256), 256, 0, st>>>(S.lines, S.obase, (uint32_t)g1, P->max_len, c2b, d_off_known,
+                ProfScope ps(c, PC_WALK, (S.n - R) * (32 + 2) * (g1 - g0) / R);
+                walk_kernel<<<div_up(g1 - g0, 256), 256, 0, st>>>(S.lines, S.super, S.obase, (uint32_t)g1, P->max_len, c2b, d_off_known,
                                                                  d_out_bases, d_out_quals, nullptr, (uint32_t)g0);
                 BFQ_CUDA(cudaGetLastError());
             }
@@ -365,8 +360,8 @@ void rebuild_dev(bfq_ctx *c, const SmoothResult &S, const bfq_params *P, const u
     const uint32_t nblk = div_up(R, 1024);
     unsigned long long *blk = arena_alloc<unsigned long long>(c, nblk + 1);
     {
-        ProfScope ps(c, PC_WALK, (S.n - R) * (64 + 2));
-        walk_kernel<<<div_up(R, 256), 256, 0, st>>>(S.lines, S.obase, (uint32_t)R, P->max_len, c2b, nullptr, sb, sq, lens);
+        ProfScope ps(c, PC_WALK, (S.n - R) * (32 + 2));
+        walk_kernel<<<div_up(R, 256), 256, 0, st>>>(S.lines, S.super, S.obase, (uint32_t)R, P->max_len, c2b, nullptr, sb, sq, lens);
         BFQ_CUDA(cudaGetLastError());
     }
     {

@@ -154,8 +154,7 @@ rank_scan_kernel(uint32_t *__restrict__ blk_counts, uint32_t nblk, const uint32_
 }
 
 __global__ void __launch_bounds__(RK_THREADS)
-rank_build_kernel(const uint8_t *__restrict__ bwt, uint64_t n, const uint32_t *__restrict__ blk_base,
-                  uint8_t *__restrict__ lines)
+rank_build_kernel(const uint8_t *__restrict__ bwt, uint64_t n, uint8_t *__restrict__ lines)
 {
     __shared__ uint8_t s_lut[256];
     __shared__ uint32_t s_warp[RK_THREADS / 32][5];
@@ -175,44 +174,29 @@ rank_build_kernel(const uint8_t *__restrict__ bwt, uint64_t n, const uint32_t *_
     }
     __syncthreads();
     if (row0 >= n) return;
+    uint32_t lo[5], hi[5];                      // occurrences inside this block before each of the thread's two sectors
 #pragma unroll
     for (int k = 0; k < 5; k++) {
-        uint32_t add = blk_base[(size_t)blockIdx.x * 8 + k];
+        uint32_t add = 0;
         for (int j = 0; j < w; j++) add += s_warp[j][k];
-        excl[k] += add;
+        const uint32_t c = k + 1;
+        const uint32_t mm = ((c & 1) ? plane[0] : ~plane[0]) & ((c & 2) ? plane[1] : ~plane[1]) & ((c & 4) ? plane[2] : ~plane[2]);
+        lo[k] = excl[k] + add;
+        hi[k] = lo[k] + __popc(mm & 0xFFFFu);
     }
-    uint4 *L = reinterpret_cast<uint4 *>(lines + (row0 >> 5) * 64);
-    L[0] = make_uint4(excl[0], excl[1], excl[2], excl[3]);
-    L[1] = make_uint4(excl[4], plane[0], plane[1], plane[2]);
+    uint8_t *S = lines + (row0 >> 4) * 32;
+    *reinterpret_cast<uint4 *>(S) = make_uint4(lo[0] | (lo[1] << 16), lo[2] | (lo[3] << 16), lo[4] | ((plane[0] & 0xFFFFu) << 16),
+                                               (plane[1] & 0xFFFFu) | ((plane[2] & 0xFFFFu) << 16));
+    *reinterpret_cast<uint4 *>(S + 32) = make_uint4(hi[0] | (hi[1] << 16), hi[2] | (hi[3] << 16), hi[4] | ((plane[0] >> 16) << 16),
+                                                    (plane[1] >> 16) | ((plane[2] >> 16) << 16));
 }
 
 // ------------------------------------------------------------------ line access helpers
-struct LineHdr { uint32_t cnt[5]; uint32_t plane[3]; };
-
-__device__ __forceinline__ LineHdr load_hdr(const uint8_t *__restrict__ lines, uint64_t row)
-{
-    const uint4 *L = reinterpret_cast<const uint4 *>(lines + (row >> 5) * 64);
-    uint4 a = L[0], b = L[1];
-    LineHdr h;
-    h.cnt[0] = a.x; h.cnt[1] = a.y; h.cnt[2] = a.z; h.cnt[3] = a.w; h.cnt[4] = b.x;
-    h.plane[0] = b.y; h.plane[1] = b.z; h.plane[2] = b.w;
-    return h;
-}
-__device__ __forceinline__ uint32_t hdr_code(const LineHdr &h, uint32_t r)
-{
-    return ((h.plane[0] >> r) & 1u) | (((h.plane[1] >> r) & 1u) << 1) | (((h.plane[2] >> r) & 1u) << 2);
-}
-__device__ __forceinline__ uint32_t hdr_lf(const LineHdr &h, uint32_t r, uint32_t c)   // c in 1..5
-{
-    uint32_t mm = ((c & 1) ? h.plane[0] : ~h.plane[0]) & ((c & 2) ? h.plane[1] : ~h.plane[1]) &
-                  ((c & 4) ? h.plane[2] : ~h.plane[2]);
-    return h.cnt[c - 1] + __popc(mm & ((1u << r) - 1u));
-}
 // where the stored quality of a row lives: inside its walk line, or (FLAT, fused pipeline with the suffix
 // array at hand: no walk lines are built) in a plain per-row array
 template <bool FLAT> __device__ __forceinline__ uint8_t *q_slot(uint8_t *lines, uint64_t row)
 {
-    return FLAT ? lines + row : lines + (row >> 5) * 64 + 32 + (row & 31);
+    return FLAT ? lines + row : ws_q(lines, row);
 }
 
 // ------------------------------------------------------------------ cluster rules (shared)
@@ -587,7 +571,7 @@ template <bool FLAT>
 __global__ void __launch_bounds__(256)
 rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8_t *__restrict__ obase,
               SmoothLists L, const uint8_t *__restrict__ bwt, const void *__restrict__ SA, int sa_wide,
-              const uint64_t *__restrict__ T3)
+              const uint64_t *__restrict__ T3, const uint32_t *__restrict__ super)
 {
     __shared__ uint32_t s_stats[ST_COUNT];
     __shared__ uint8_t s_lut[256];
@@ -597,18 +581,15 @@ rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8
     __syncthreads();
     auto row_code = [&](uint64_t i) -> uint32_t {
         if (FLAT) return s_lut[bwt[i]];
-        LineHdr h = load_hdr(lines, i);
-        return hdr_code(h, (uint32_t)(i & 31));
+        return ws_code(ws_load(lines, i), (uint32_t)(i & 15));
     };
     auto prec_code = [&](uint64_t i, uint32_t c) -> uint32_t {      // symbol before row i's symbol c in its read
         if (FLAT) {
             const uint64_t p = sa_wide ? ((const uint64_t *)SA)[i] : (uint64_t)((const uint32_t *)SA)[i];
             return p >= 2 ? sym_code(T3, p - 2) : 0u;
         }
-        LineHdr h = load_hdr(lines, i);
-        const uint64_t r = hdr_lf(h, (uint32_t)(i & 31), c);
-        LineHdr h2 = load_hdr(lines, r);
-        return hdr_code(h2, (uint32_t)(r & 31));
+        const uint64_t r = ws_lf(ws_load(lines, i), super, i, c);
+        return ws_code(ws_load(lines, r), (uint32_t)(r & 15));
     };
     uint32_t st[ST_COUNT];
 #pragma unroll
@@ -734,17 +715,19 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     BFQ_CUDA(cudaStreamSynchronize(st));     // the pageable/pinned staging above is reused by later calls
 
     // ---- walk lines (computeVectorUnbuildBCR, decode.cpp:87-235, + tableOcc)
-    const uint64_t nlines = (n + 31) / 32;
+    static_assert(RK_ROWS == (1 << WS_SUPER_SHIFT), "a rank block is one super-block of the walk sectors");
+    const uint64_t nlines = (n + 31) / 32;                 // two 32-byte sectors each
     out->lines = flat ? arena_alloc<uint8_t>(c, n + 64) : arena_alloc<uint8_t>(c, nlines * 64 + 64);
     out->obase = arena_alloc<uint8_t>(c, n + 64);
+    const uint32_t nblk = div_up(n, RK_ROWS);
+    uint32_t *blk = flat ? nullptr : arena_alloc<uint32_t>(c, (size_t)nblk * 8);       // stays: the super-block table
+    out->super = blk;
     Arena::Mark mk = c->arena.mark();
     if (!flat) {
-        const uint32_t nblk = div_up(n, RK_ROWS);
-        uint32_t *blk = arena_alloc<uint32_t>(c, (size_t)nblk * 8);
         ProfScope ps(c, PC_RANK, 2 * n + nlines * 32, 3);
         rank_count_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, blk);
         rank_scan_kernel<<<1, 1024, 0, st>>>(blk, nblk, d_pile);
-        rank_build_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, blk, out->lines);
+        rank_build_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, out->lines);
         launch_check(c);
     }
 
@@ -773,8 +756,8 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     }
     {
         ProfScope ps(c, PC_RULE11, 0);
-        if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, sa_wide ? 1 : 0, d_t3);
-        else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, 0, d_t3);
+        if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, sa_wide ? 1 : 0, d_t3, nullptr);
+        else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, 0, d_t3, out->super);
         launch_check(c);
     }
     fetch_small(c, c->h_small, d_stats, (ST_COUNT + 2) * 8);
