@@ -254,6 +254,85 @@ int bfq_pipeline(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const
     API_END
 }
 
+// ---- FASTQ text in / FASTQ text out: parsing and record assembly on the device
+int bfq_build_ebwt_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, uint8_t eos_byte, uint8_t *bwt, uint8_t *qs,
+                         uint8_t *lcp, uint64_t capacity, uint64_t *nreads_out, uint64_t *n_out)
+{
+    API_BEGIN
+    if (!nreads_out || !n_out || (size && (!text || !bwt || !qs || !lcp))) BFQ_FAIL(BFQ_EINVAL, "bfq_build_ebwt_fastq: null pointer");
+    *nreads_out = 0; *n_out = 0;
+    uint8_t *d_text = to_device(ctx, text, size, 64);
+    DeviceReads R;
+    fastq_ingest_dev(ctx, d_text, size, &R);
+    const uint64_t N = R.total + R.nreads;
+    *nreads_out = R.nreads; *n_out = N;
+    if (N == 0) { BFQ_CUDA(cudaStreamSynchronize(ctx->stream)); return BFQ_OK; }
+    if (N > capacity) BFQ_FAIL(BFQ_ECAPACITY, "the collection has %llu rows, the output buffers hold %llu", (unsigned long long)N, (unsigned long long)capacity);
+    uint64_t mn, mx;
+    check_reads_dev(ctx, R.off, R.nreads, R.total, &mn, &mx);
+    uint8_t *d_bwt = arena_alloc<uint8_t>(ctx, N + 64), *d_qs = arena_alloc<uint8_t>(ctx, N + 64), *d_lcp = arena_alloc<uint8_t>(ctx, N + 64);
+    build_ebwt_dev(ctx, R.bases, R.quals, R.off, R.nreads, R.total, mx, eos_byte, d_bwt, d_qs, d_lcp, nullptr);
+    BFQ_CUDA(cudaMemcpyAsync(bwt, d_bwt, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(qs, d_qs, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaMemcpyAsync(lcp, d_lcp, N, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    API_END
+}
+
+int bfq_smooth_rebuild_fastq(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, const uint8_t *lcp, uint64_t n,
+                             const bfq_params *params, uint8_t *fastq_out, uint64_t capacity, uint64_t *fastq_size,
+                             bfq_stats *stats)
+{
+    API_BEGIN
+    if (!params || !fastq_size || (n && (!bwt || !qs || !lcp || !fastq_out))) BFQ_FAIL(BFQ_EINVAL, "bfq_smooth_rebuild_fastq: null pointer");
+    if (stats) memset(stats, 0, sizeof *stats);
+    *fastq_size = 0;
+    if (n == 0) return BFQ_OK;
+    uint8_t *d_bwt = to_device(ctx, bwt, n, 64), *d_qs = to_device(ctx, qs, n, 64), *d_lcp = to_device(ctx, lcp, n, 64);
+    SmoothResult S;
+    smooth_dev(ctx, d_bwt, d_qs, d_lcp, n, params, &S, stats);
+    uint8_t *d_ob = arena_alloc<uint8_t>(ctx, n + 64), *d_oq = arena_alloc<uint8_t>(ctx, n + 64);
+    uint64_t *d_oo = arena_alloc<uint64_t>(ctx, S.nreads + 1);
+    uint64_t total = 0;
+    rebuild_dev(ctx, S, params, nullptr, d_ob, d_oq, d_oo, &total);
+    const uint64_t fsz = 2 * total + 6 * S.nreads;
+    if (fsz > capacity) BFQ_FAIL(BFQ_ECAPACITY, "the FASTQ text takes %llu bytes, the buffer holds %llu", (unsigned long long)fsz, (unsigned long long)capacity);
+    uint8_t *d_text = arena_alloc<uint8_t>(ctx, fsz + 64);
+    fastq_emit_dev(ctx, d_ob, d_oq, d_oo, S.nreads, total, d_text);
+    if (fsz) BFQ_CUDA(cudaMemcpyAsync(fastq_out, d_text, fsz, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    *fastq_size = fsz;
+    remember(ctx, S);
+    API_END
+}
+
+int bfq_pipeline_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, const bfq_params *params, uint8_t *bwt, uint8_t *qs,
+                       uint8_t *lcp, uint64_t capacity, uint8_t *fastq_out, uint64_t fastq_capacity, uint64_t *fastq_size,
+                       uint64_t *nreads_out, uint64_t *n_out, bfq_stats *stats)
+{
+    API_BEGIN
+    if (!params || !fastq_size || !nreads_out || !n_out || (size && (!text || !fastq_out))) BFQ_FAIL(BFQ_EINVAL, "bfq_pipeline_fastq: null pointer");
+    if (stats) memset(stats, 0, sizeof *stats);
+    *fastq_size = 0; *nreads_out = 0; *n_out = 0;
+    uint8_t *d_text = to_device(ctx, text, size, 64);
+    DeviceReads R;
+    fastq_ingest_dev(ctx, d_text, size, &R);
+    const uint64_t N = R.total + R.nreads, fsz = 2 * R.total + 6 * R.nreads;
+    *nreads_out = R.nreads; *n_out = N;
+    if (N == 0) { BFQ_CUDA(cudaStreamSynchronize(ctx->stream)); return BFQ_OK; }
+    if ((bwt || qs || lcp) && N > capacity) BFQ_FAIL(BFQ_ECAPACITY, "the collection has %llu rows, the output buffers hold %llu", (unsigned long long)N, (unsigned long long)capacity);
+    if (fsz > fastq_capacity) BFQ_FAIL(BFQ_ECAPACITY, "the FASTQ text takes %llu bytes, the buffer holds %llu", (unsigned long long)fsz, (unsigned long long)fastq_capacity);
+    uint8_t *d_ob = arena_alloc<uint8_t>(ctx, R.total + 64), *d_oq = arena_alloc<uint8_t>(ctx, R.total + 64);
+    // the input text is dead once the reads are parsed, but it sits below them on the arena stack: the output text gets its own block
+    uint8_t *d_out = arena_alloc<uint8_t>(ctx, fsz + 64);
+    pipeline_dev(ctx, R.bases, R.quals, R.off, R.nreads, R.total, params, nullptr, nullptr, nullptr, d_ob, d_oq, stats, bwt, qs, lcp);
+    fastq_emit_dev(ctx, d_ob, d_oq, R.off, R.nreads, R.total, d_out);
+    BFQ_CUDA(cudaMemcpyAsync(fastq_out, d_out, fsz, cudaMemcpyDeviceToHost, ctx->stream));
+    BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
+    *fastq_size = fsz;
+    API_END
+}
+
 int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off,
                      uint64_t nreads, uint64_t total_bases, const bfq_params *params, uint8_t *d_bwt,
                      uint8_t *d_qs, uint8_t *d_lcp, uint8_t *d_out_bases, uint8_t *d_out_quals, bfq_stats *stats)

@@ -250,6 +250,19 @@ void build_ebwt_dev_wide(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
                          uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp, uint64_t *d_sa_out, uint64_t *d_t3_keep,
                          KeyRange *range);       // 64-bit text positions; key ranges only
 size_t packed_text_words(uint64_t N);     // u64 words build_ebwt_dev needs for the packed text of N rows
+// fastq.cu
+struct DeviceReads {             // reads parsed on the device (arena memory)
+    uint8_t *bases = nullptr, *quals = nullptr;
+    uint64_t *off = nullptr;      // nreads + 1
+    uint64_t nreads = 0, total = 0;
+};
+// FASTQ text (device) -> flat reads: line 2 / line 4 of every 4-line record, empty reads dropped, trailing partial record ignored
+void fastq_ingest_dev(bfq_ctx *c, const uint8_t *d_text, uint64_t size, DeviceReads *out);
+// flat reads -> FASTQ text with "@" headers; d_text holds 2 * total + 6 * nreads bytes
+void fastq_emit_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off, uint64_t nreads,
+                    uint64_t total, uint8_t *d_text);
+// rebuild.cu: exclusive scan u32 -> u64, out[n] = total
+void scan_u32_u64_dev(bfq_ctx *c, const uint32_t *in, uint64_t n, unsigned long long *out);
 // smooth.cu
 struct SmoothResult {
     uint8_t *lines = nullptr;     // walk sectors: 32 B per 16 rows (see ws_load)

@@ -125,6 +125,17 @@ __global__ void __launch_bounds__(256) scan_down_kernel(const uint32_t *in, uint
     if (blockIdx.x == 0 && tid == 0) out[n] = *total;
 }
 
+void scan_u32_u64_dev(bfq_ctx *c, const uint32_t *in, uint64_t n, unsigned long long *out)
+{
+    if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "scan of %llu elements", (unsigned long long)n);
+    const uint32_t nblk = div_up(n, 1024);
+    unsigned long long *blk = arena_alloc<unsigned long long>(c, (size_t)nblk + 2);
+    scan_reduce_kernel<<<nblk, 256, 0, c->stream>>>(in, (uint32_t)n, blk);
+    scan_blocks_kernel<<<1, 1024, 0, c->stream>>>(blk, nblk, blk + nblk);
+    scan_down_kernel<<<nblk, 256, 0, c->stream>>>(in, (uint32_t)n, blk, out, blk + nblk);
+    BFQ_CUDA(cudaGetLastError());
+}
+
 // one warp per read: reverse the walk-order scratch into the final position
 __global__ void __launch_bounds__(256)
 assemble_kernel(const uint8_t *__restrict__ sb, const uint8_t *__restrict__ sq, const uint32_t *__restrict__ lens,

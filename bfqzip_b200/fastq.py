@@ -17,8 +17,8 @@ def parse_fastq_bytes(data: bytes):
         lines.pop()
     nrec = len(lines) // 4
     headers = lines[0:4 * nrec:4]
-    seqs = lines[1:4 * nrec:4]
-    quals = lines[3:4 * nrec:4]
+    seqs = [s[:-1] if s.endswith(b"\r") else s for s in lines[1:4 * nrec:4]]       # CR before LF is not part of the read
+    quals = [s[:-1] if s.endswith(b"\r") else s for s in lines[3:4 * nrec:4]]
     lens = np.fromiter((len(s) for s in seqs), dtype=np.int64, count=nrec)
     off = np.zeros(nrec + 1, dtype=np.uint64)
     np.cumsum(lens, out=off[1:].view(np.int64))

@@ -176,6 +176,41 @@ class BfqGpu:
                                             _ptr(d_out_quals), C.byref(st)))
         return st.as_dict()
 
+    # ---- FASTQ text on either side (parsed / written on the device)
+    def build_ebwt_fastq(self, text: bytes, eos=35):
+        buf = np.frombuffer(text, np.uint8)
+        cap = max(1, len(buf) // 2)
+        bwt = np.empty(cap, np.uint8); qs = np.empty(cap, np.uint8); lcp = np.empty(cap, np.uint8)
+        nreads = C.c_uint64(0); n = C.c_uint64(0)
+        self._chk(self.lib.bfq_build_ebwt_fastq(self.h, _ptr(buf), C.c_uint64(len(buf)), C.c_uint8(eos), _ptr(bwt), _ptr(qs),
+                                                _ptr(lcp), C.c_uint64(cap), C.byref(nreads), C.byref(n)))
+        k = int(n.value)
+        return bwt[:k], qs[:k], lcp[:k], int(nreads.value)
+
+    def smooth_rebuild_fastq(self, bwt, qs, lcp, params: Params):
+        n = len(bwt)
+        cap = 6 * n + 64                       # 2 T + 6 R bytes for T bases in R reads, n = T + R
+        out = np.empty(cap, np.uint8)
+        size = C.c_uint64(0); st = Stats()
+        self._chk(self.lib.bfq_smooth_rebuild_fastq(self.h, _ptr(bwt), _ptr(qs), _ptr(lcp), C.c_uint64(n), C.byref(params),
+                                                    _ptr(out), C.c_uint64(cap), C.byref(size), C.byref(st)))
+        return out[:int(size.value)].tobytes(), st.as_dict()
+
+    def pipeline_fastq(self, text: bytes, params: Params, want_files=True):
+        buf = np.frombuffer(text, np.uint8)
+        cap = max(1, len(buf) // 2)
+        bwt = np.empty(cap, np.uint8) if want_files else None
+        qs = np.empty(cap, np.uint8) if want_files else None
+        lcp = np.empty(cap, np.uint8) if want_files else None
+        out = np.empty(len(buf) + len(buf) // 4 + 64, np.uint8)
+        size = C.c_uint64(0); nreads = C.c_uint64(0); n = C.c_uint64(0); st = Stats()
+        self._chk(self.lib.bfq_pipeline_fastq(self.h, _ptr(buf), C.c_uint64(len(buf)), C.byref(params), _ptr(bwt), _ptr(qs), _ptr(lcp),
+                                              C.c_uint64(cap), _ptr(out), C.c_uint64(len(out)), C.byref(size), C.byref(nreads),
+                                              C.byref(n), C.byref(st)))
+        k = int(n.value)
+        files = (bwt[:k], qs[:k], lcp[:k]) if want_files else None
+        return files, out[:int(size.value)].tobytes(), st.as_dict()
+
     # ---- one collection over several GPUs (bfq_dist_build / bfq_dist_place)
     def dist_build(self, d_bases, d_quals, d_off, nreads, total_bases, params: Params, rank, world, capacity,
                    text_bounds, d_bwt, d_qs, d_lcp, d_keys, d_vals):

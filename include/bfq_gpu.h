@@ -123,6 +123,29 @@ int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_qual
                      const bfq_params *params, uint8_t *d_bwt, uint8_t *d_qs, uint8_t *d_lcp,
                      uint8_t *d_out_bases, uint8_t *d_out_quals, bfq_stats *stats);
 
+/* ---- FASTQ text in, FASTQ text out ----------------------------
+ * The same three calls with the FASTQ file contents on either side instead of flat arrays: the
+ * newline scan and field split of the loaders (external/gsufsort/lib/file.c:182-275 keeps line 2
+ * and line 4 of every 4-line record; empty reads are dropped, lib/utils.c:229-236; a trailing
+ * partial record is ignored; '\r' before '\n' is stripped) and the record writer of step 3
+ * (src_ext_mem/decode.cpp:1080-1127: "@\nBASES\n+\nQUALS\n", header "@" alone -- use the flat calls
+ * for -H header files) run on the device.  text: host pointer (pageable or pinned) to `size` bytes.
+ * bwt/qs/lcp hold `capacity` bytes each; size / 2 always suffices.  The FASTQ written for a
+ * collection of R reads and T bases takes 2 T + 6 R bytes; `size` always suffices when it is the
+ * text the reads came from.  Errors: BFQ_EINVAL for a record whose two payload lines differ in
+ * length, BFQ_ECAPACITY when an output buffer is too small (the needed size is in the message). */
+int bfq_build_ebwt_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, uint8_t eos_byte,
+                         uint8_t *bwt, uint8_t *qs, uint8_t *lcp, uint64_t capacity,
+                         uint64_t *nreads, uint64_t *n);
+int bfq_smooth_rebuild_fastq(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, const uint8_t *lcp,
+                             uint64_t n, const bfq_params *params, uint8_t *fastq_out,
+                             uint64_t capacity, uint64_t *fastq_size, bfq_stats *stats);
+/* bwt/qs/lcp may be NULL (then they are not produced on the host). */
+int bfq_pipeline_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, const bfq_params *params,
+                       uint8_t *bwt, uint8_t *qs, uint8_t *lcp, uint64_t capacity,
+                       uint8_t *fastq_out, uint64_t fastq_capacity, uint64_t *fastq_size,
+                       uint64_t *nreads, uint64_t *n, bfq_stats *stats);
+
 /* ---- one collection over several GPUs (second row) ----------------
  * Every rank holds the whole collection (device pointers as in bfq_pipeline_dev) and builds the
  * slice [row_base, row_base + n_local) of the global eBWT / QS / LCP: the suffixes whose first four
