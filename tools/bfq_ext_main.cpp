@@ -121,15 +121,24 @@ int main(int argc, char **argv)
         }
         uint64_t nreads = 0;
         for (uint64_t i = 0; i < n; i++) nreads += fb.data[i] == P.eos_byte;     // numSeq (bfq_ext.cpp:160-166)
-        std::vector<uint8_t> ob(n ? n : 1), oq(n ? n : 1);
-        std::vector<uint64_t> off(nreads + 1);
+        // Without a header file the records ("@" headers) are assembled on the device and arrive as the text of OUT.fq;
+        // with -H the flat reads come back and the records are formatted here around the caller's header lines.
+        const bool device_emit = !headers && !getenv("BFQ_HOST_EMIT");
+        const uint64_t text_cap = device_emit ? 2 * (n - nreads) + 6 * nreads + 64 : 1;
+        const uint64_t flat_cap = device_emit ? 1 : (n ? n : 1);
+        std::unique_ptr<uint8_t[]> text(new uint8_t[text_cap]), ob(new uint8_t[flat_cap]), oq(new uint8_t[flat_cap]);
+        std::vector<uint64_t> off(device_emit ? 1 : nreads + 1);
+        uint64_t text_size = 0;
+        // touch the output pages now (the device is still coming up): a download into untouched memory faults page by page
+        memset(text.get(), 0, text_cap); memset(ob.get(), 0, flat_cap); memset(oq.get(), 0, flat_cap);
         auto tp = std::chrono::steady_clock::now();
         auto cr = ctx_ready.get();
         bfq_ctx *ctx = std::get<1>(cr);
         if (std::get<0>(cr) != BFQ_OK) { std::cerr << "Error: " << std::get<2>(cr) << endl; return EXIT_FAILURE; }
         bfq_stats S;
         auto t1 = std::chrono::steady_clock::now();
-        int rc = bfq_smooth_rebuild(ctx, fb.data, fq.data, fl.data, n, &P, ob.data(), oq.data(), off.data(), nreads + 1, &S);
+        int rc = device_emit ? bfq_smooth_rebuild_fastq(ctx, fb.data, fq.data, fl.data, n, &P, text.get(), text_cap, &text_size, &S)
+                             : bfq_smooth_rebuild(ctx, fb.data, fq.data, fl.data, n, &P, ob.get(), oq.get(), off.data(), nreads + 1, &S);
         if (rc != BFQ_OK) { std::cerr << "Error: " << bfq_last_error() << endl; bfq_ctx_destroy(ctx); return EXIT_FAILURE; }
         auto t2 = std::chrono::steady_clock::now();
         bfq_ctx_destroy(ctx);
@@ -144,13 +153,17 @@ int main(int argc, char **argv)
         }
         FILE *fo = fopen((output + ".fq").c_str(), "wb");
         if (!fo) { std::cerr << "Error opening \"" << output << ".fq\" file" << endl; return EXIT_FAILURE; }
-        std::vector<uint8_t> buf;
-        const uint64_t CH = 1 << 16;
-        for (uint64_t r0 = 0; r0 < nreads; r0 += CH) {
-            buf.clear();
-            bfqio::format_fastq(ob.data(), oq.data(), off.data(), r0, std::min(nreads, r0 + CH), headers ? fh->data : nullptr,
-                                headers ? hidx.data() : nullptr, buf);
-            if (fwrite(buf.data(), 1, buf.size(), fo) != buf.size()) { std::cerr << "Error writing " << output << ".fq" << endl; return EXIT_FAILURE; }
+        if (device_emit) {
+            if (text_size && fwrite(text.get(), 1, text_size, fo) != text_size) { std::cerr << "Error writing " << output << ".fq" << endl; return EXIT_FAILURE; }
+        } else {
+            std::vector<uint8_t> buf;
+            const uint64_t CH = 1 << 16;
+            for (uint64_t r0 = 0; r0 < nreads; r0 += CH) {
+                buf.clear();
+                bfqio::format_fastq(ob.get(), oq.get(), off.data(), r0, std::min(nreads, r0 + CH), headers ? fh->data : nullptr,
+                                    headers ? hidx.data() : nullptr, buf);
+                if (fwrite(buf.data(), 1, buf.size(), fo) != buf.size()) { std::cerr << "Error writing " << output << ".fq" << endl; return EXIT_FAILURE; }
+            }
         }
         if (fclose(fo) != 0) { std::cerr << "Error closing " << output << ".fq" << endl; return EXIT_FAILURE; }
         auto t3 = std::chrono::steady_clock::now();

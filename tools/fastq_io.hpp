@@ -30,7 +30,9 @@ struct MappedFile {
         if (fstat(fd, &st) != 0) { close(fd); throw std::runtime_error("cannot stat " + path); }
         size = (size_t)st.st_size;
         if (size) {
-            void *p = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+            // MAP_POPULATE: the pages are faulted in here (while the CUDA context is still coming up in its own thread),
+            // not one by one inside the upload
+            void *p = mmap(nullptr, size, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
             if (p == MAP_FAILED) { close(fd); throw std::runtime_error("cannot mmap " + path); }
             madvise(p, size, MADV_SEQUENTIAL);
             data = (const uint8_t *)p;

@@ -14,6 +14,7 @@
 #include <stdlib.h>
 #include <chrono>
 #include <future>
+#include <memory>
 #include <tuple>
 #include <string>
 
@@ -81,20 +82,35 @@ int main(int argc, char **argv)
             int rc = bfq_ctx_create(&x, device);
             return std::make_tuple(rc, x, std::string(rc == BFQ_OK ? "" : bfq_last_error()));     // the message is thread-local
         });
-        bfqio::Reads R;
-        for (auto &p : inputs) {                                // eGap concatenates its inputs into one collection
-            bfqio::MappedFile f(p);
-            bfqio::load_fastq(f, R);
-        }
-        const uint64_t nreads = R.nreads(), N = R.bases.size() + nreads;
         const uint8_t eos = gsuf ? (uint8_t)'#' : (uint8_t)0;
-        std::vector<uint8_t> bwt(N), qs(N), lcp(N);
+        // One input (what BFQzip_ext.py passes): the file goes to the device as it is and is parsed there.  Several inputs
+        // (eGap concatenates them into one collection) are parsed on the host.
+        const bool device_parse = inputs.size() == 1 && !getenv("BFQ_HOST_PARSE");
+        std::unique_ptr<bfqio::MappedFile> text;
+        bfqio::Reads R;
+        uint64_t nreads = 0, N = 0, cap = 0;
+        if (device_parse) {
+            text.reset(new bfqio::MappedFile(inputs[0]));
+            cap = text->size / 2 + 1;
+        } else {
+            for (auto &p : inputs) {
+                bfqio::MappedFile f(p);
+                bfqio::load_fastq(f, R);
+            }
+            nreads = R.nreads(); N = R.bases.size() + nreads; cap = N + 1;
+        }
+        std::unique_ptr<uint8_t[]> bwt_buf(new uint8_t[cap]), qs_buf(new uint8_t[cap]), lcp_buf(new uint8_t[cap]);
+        // touch the output pages now (the device is still coming up): a download into untouched memory faults page by page
+        memset(bwt_buf.get(), 0, cap); memset(qs_buf.get(), 0, cap); memset(lcp_buf.get(), 0, cap);
+        struct View { uint8_t *p; uint8_t *data() const { return p; } uint8_t operator[](uint64_t i) const { return p[i]; } } bwt{bwt_buf.get()}, qs{qs_buf.get()}, lcp{lcp_buf.get()};
         auto tp = std::chrono::steady_clock::now();
         auto cr = ctx_ready.get();
         bfq_ctx *ctx = std::get<1>(cr);
         if (std::get<0>(cr) != BFQ_OK) die(std::get<2>(cr).c_str());
         auto t1 = std::chrono::steady_clock::now();
-        int rc = bfq_build_ebwt(ctx, R.bases.data(), R.quals.data(), R.off.data(), nreads, eos, bwt.data(), qs.data(), lcp.data());
+        int rc = device_parse
+                     ? bfq_build_ebwt_fastq(ctx, text->data, text->size, eos, bwt.data(), qs.data(), lcp.data(), cap, &nreads, &N)
+                     : bfq_build_ebwt(ctx, R.bases.data(), R.quals.data(), R.off.data(), nreads, eos, bwt.data(), qs.data(), lcp.data());
         if (rc != BFQ_OK) die(bfq_last_error());
         auto t2 = std::chrono::steady_clock::now();
         bfq_ctx_destroy(ctx);
@@ -113,7 +129,7 @@ int main(int argc, char **argv)
         }
         auto t3 = std::chrono::steady_clock::now();
         auto sec = [](auto a, auto b) { return std::chrono::duration<double>(b - a).count(); };
-        printf("%s (GPU): %llu reads, %llu symbols; load %.3f s (parse %.3f s, device ready after %.3f s), eBWT+QS+LCP %.3f s, write %.3f s\n", gsuf ? "gsufsort" : "eGap",
+        printf("%s (GPU): %llu reads, %llu symbols; load %.3f s (inputs %.3f s, device ready after %.3f s), eBWT+QS+LCP %.3f s, write %.3f s\n", gsuf ? "gsufsort" : "eGap",
                (unsigned long long)nreads, (unsigned long long)N, sec(t0, t1), sec(t0, tp), sec(t0, t1), sec(t1, t2), sec(t2, t3));
         (void)verbose;
     } catch (std::exception &e) {
