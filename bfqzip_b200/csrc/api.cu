@@ -281,7 +281,7 @@ int bfq_build_ebwt_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, uint8
 
 int bfq_smooth_rebuild_fastq(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, const uint8_t *lcp, uint64_t n,
                              const bfq_params *params, uint8_t *fastq_out, uint64_t capacity, uint64_t *fastq_size,
-                             bfq_stats *stats)
+                             uint8_t *dna_out, uint8_t *qs_out, bfq_stats *stats)
 {
     API_BEGIN
     if (!params || !fastq_size || (n && (!bwt || !qs || !lcp || !fastq_out))) BFQ_FAIL(BFQ_EINVAL, "bfq_smooth_rebuild_fastq: null pointer");
@@ -297,9 +297,15 @@ int bfq_smooth_rebuild_fastq(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs
     rebuild_dev(ctx, S, params, nullptr, d_ob, d_oq, d_oo, &total);
     const uint64_t fsz = 2 * total + 6 * S.nreads;
     if (fsz > capacity) BFQ_FAIL(BFQ_ECAPACITY, "the FASTQ text takes %llu bytes, the buffer holds %llu", (unsigned long long)fsz, (unsigned long long)capacity);
+    if ((dna_out == nullptr) != (qs_out == nullptr)) BFQ_FAIL(BFQ_EINVAL, "bfq_smooth_rebuild_fastq: dna_out and qs_out come together");
     uint8_t *d_text = arena_alloc<uint8_t>(ctx, fsz + 64);
-    fastq_emit_dev(ctx, d_ob, d_oq, d_oo, S.nreads, total, d_text);
+    uint8_t *d_dna = dna_out ? arena_alloc<uint8_t>(ctx, n + 64) : nullptr, *d_qsl = dna_out ? arena_alloc<uint8_t>(ctx, n + 64) : nullptr;
+    fastq_emit_dev(ctx, d_ob, d_oq, d_oo, S.nreads, total, d_text, d_dna, d_qsl);
     if (fsz) BFQ_CUDA(cudaMemcpyAsync(fastq_out, d_text, fsz, cudaMemcpyDeviceToHost, ctx->stream));
+    if (dna_out) {          // the rebuilt reads keep their lengths: total + nreads == n
+        BFQ_CUDA(cudaMemcpyAsync(dna_out, d_dna, total + S.nreads, cudaMemcpyDeviceToHost, ctx->stream));
+        BFQ_CUDA(cudaMemcpyAsync(qs_out, d_qsl, total + S.nreads, cudaMemcpyDeviceToHost, ctx->stream));
+    }
     BFQ_CUDA(cudaStreamSynchronize(ctx->stream));
     *fastq_size = fsz;
     remember(ctx, S);

@@ -260,7 +260,8 @@ struct DeviceReads {             // reads parsed on the device (arena memory)
 void fastq_ingest_dev(bfq_ctx *c, const uint8_t *d_text, uint64_t size, DeviceReads *out);
 // flat reads -> FASTQ text with "@" headers; d_text holds 2 * total + 6 * nreads bytes
 void fastq_emit_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off, uint64_t nreads,
-                    uint64_t total, uint8_t *d_text);
+                    uint64_t total, uint8_t *d_text, uint8_t *d_dna = nullptr, uint8_t *d_qs = nullptr);
+// d_dna / d_qs (both or none, total + nreads bytes each): line 2 / line 4 of every record, one per line
 // rebuild.cu: exclusive scan u32 -> u64, out[n] = total
 void scan_u32_u64_dev(bfq_ctx *c, const uint32_t *in, uint64_t n, unsigned long long *out);
 // smooth.cu

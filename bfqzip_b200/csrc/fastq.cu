@@ -158,7 +158,7 @@ void fastq_ingest_dev(bfq_ctx *c, const uint8_t *d_text, uint64_t size, DeviceRe
 // record g starts at 2 * off[g] + 6 * g: '@' '\n' bases '\n' '+' '\n' quals '\n'
 __global__ void __launch_bounds__(256)
 fastq_emit_kernel(const uint8_t *__restrict__ bases, const uint8_t *__restrict__ quals, const uint64_t *__restrict__ off,
-                  uint64_t nreads, uint8_t *__restrict__ text)
+                  uint64_t nreads, uint8_t *__restrict__ text, uint8_t *__restrict__ dna, uint8_t *__restrict__ qsl)
 {
     const int lane = threadIdx.x & 31;
     const uint64_t warp0 = ((uint64_t)blockIdx.x * 256 + threadIdx.x) >> 5, nwarps = ((uint64_t)gridDim.x * 256) >> 5;
@@ -167,16 +167,22 @@ fastq_emit_kernel(const uint8_t *__restrict__ bases, const uint8_t *__restrict__
         uint8_t *o = text + 2 * s + 6 * g;
         if (lane == 0) { o[0] = '@'; o[1] = '\n'; o[2 + l] = '\n'; o[3 + l] = '+'; o[4 + l] = '\n'; o[5 + 2 * l] = '\n'; }
         for (uint64_t j = lane; j < l; j += 32) { o[2 + j] = bases[s + j]; o[5 + l + j] = quals[s + j]; }
+        if (dna) {
+            // the component streams of step 4 (BFQzip_ext.py:224-244: sed -n 2~4p / 4~4p): one line per read
+            for (uint64_t j = lane; j < l; j += 32) { dna[s + g + j] = bases[s + j]; qsl[s + g + j] = quals[s + j]; }
+            if (lane == 0) { dna[s + g + l] = '\n'; qsl[s + g + l] = '\n'; }
+        }
     }
 }
 
 void fastq_emit_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_quals, const uint64_t *d_off, uint64_t nreads,
-                    uint64_t total, uint8_t *d_text)
+                    uint64_t total, uint8_t *d_text, uint8_t *d_dna, uint8_t *d_qs)
 {
     if (nreads == 0) return;
+    if ((d_dna == nullptr) != (d_qs == nullptr)) BFQ_FAIL(BFQ_EINVAL, "the two component streams come together");
     ProfScope ps(c, PC_ASSEMBLE, 4 * total + 6 * nreads);
     int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 16, div_up(nreads * 32, 256));
-    fastq_emit_kernel<<<std::max(grid, 1), 256, 0, c->stream>>>(d_bases, d_quals, d_off, nreads, d_text);
+    fastq_emit_kernel<<<std::max(grid, 1), 256, 0, c->stream>>>(d_bases, d_quals, d_off, nreads, d_text, d_dna, d_qs);
     BFQ_CUDA(cudaGetLastError());
 }
 

@@ -187,14 +187,21 @@ class BfqGpu:
         k = int(n.value)
         return bwt[:k], qs[:k], lcp[:k], int(nreads.value)
 
-    def smooth_rebuild_fastq(self, bwt, qs, lcp, params: Params):
+    def smooth_rebuild_fastq(self, bwt, qs, lcp, params: Params, components=False):
         n = len(bwt)
+        dna = np.empty(n + 1, np.uint8) if components else None
+        qsl = np.empty(n + 1, np.uint8) if components else None
         cap = 6 * n + 64                       # 2 T + 6 R bytes for T bases in R reads, n = T + R
         out = np.empty(cap, np.uint8)
         size = C.c_uint64(0); st = Stats()
         self._chk(self.lib.bfq_smooth_rebuild_fastq(self.h, _ptr(bwt), _ptr(qs), _ptr(lcp), C.c_uint64(n), C.byref(params),
-                                                    _ptr(out), C.c_uint64(cap), C.byref(size), C.byref(st)))
-        return out[:int(size.value)].tobytes(), st.as_dict()
+                                                    _ptr(out), C.c_uint64(cap), C.byref(size), _ptr(dna), _ptr(qsl), C.byref(st)))
+        text = out[:int(size.value)].tobytes()
+        if components:
+            r = text.count(b"\n") // 4
+            k = (len(text) - 6 * r) // 2 + r                      # bases + one newline per read
+            return text, st.as_dict(), dna[:k].tobytes(), qsl[:k].tobytes()
+        return text, st.as_dict()
 
     def pipeline_fastq(self, text: bytes, params: Params, want_files=True):
         buf = np.frombuffer(text, np.uint8)

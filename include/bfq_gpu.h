@@ -139,7 +139,12 @@ int bfq_build_ebwt_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, uint8
                          uint64_t *nreads, uint64_t *n);
 int bfq_smooth_rebuild_fastq(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, const uint8_t *lcp,
                              uint64_t n, const bfq_params *params, uint8_t *fastq_out,
-                             uint64_t capacity, uint64_t *fastq_size, bfq_stats *stats);
+                             uint64_t capacity, uint64_t *fastq_size, uint8_t *dna_out,
+                             uint8_t *qs_out, bfq_stats *stats);
+/* dna_out / qs_out (both or NULL, n bytes each; section 8(f) row 2): the component streams step 4
+ * makes with `sed -n 2~4p` / `sed -n 4~4p` (BFQzip_ext.py:19-21, 224-244) -- line 2 / line 4 of every
+ * record of the FASTQ just written, one per line -- straight from the device buffers.  They take
+ * at most n bytes (bases + one newline per read; fewer when -l truncates reads). */
 /* bwt/qs/lcp may be NULL (then they are not produced on the host). */
 int bfq_pipeline_fastq(bfq_ctx *ctx, const uint8_t *text, uint64_t size, const bfq_params *params,
                        uint8_t *bwt, uint8_t *qs, uint8_t *lcp, uint64_t capacity,

@@ -76,6 +76,11 @@ def test_emit_matches_host_writer(g):
     ob, oq, ooff, st = g.smooth_rebuild(bwt, qs, lcp, P)
     text, st2 = g.smooth_rebuild_fastq(bwt, qs, lcp, P)
     assert text == fastq.format_fastq(ob, oq, ooff) and st2 == st
+    # the component streams of step 4: sed -n 2~4p / sed -n 4~4p of the FASTQ just written
+    text3, _, dna, qsl = g.smooth_rebuild_fastq(bwt, qs, lcp, P, components=True)
+    lines = text.split(b"\n")
+    assert text3 == text
+    assert dna == b"".join(x + b"\n" for x in lines[1::4]) and qsl == b"".join(x + b"\n" for x in lines[3::4])
 
 
 def test_pipeline_fastq_text_to_text(g):

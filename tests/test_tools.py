@@ -103,3 +103,29 @@ def test_bfq_ext_modes_vs_oracle(tmp_path, mode):
     assert open(out + ".fq", "rb").read() == fastq.format_fastq(b, q, o)
     got = H.parse_ref_stats(r.stdout.decode())
     assert all(got[k] == st[k] for k in got)
+
+
+@pytest.mark.gpu
+def test_bfq_ext_component_streams_and_host_paths(tmp_path):
+    """-C writes OUT.fq.dna / OUT.fq.qs = `sed -n 2~4p` / `sed -n 4~4p` of OUT.fq (step 4's streams, BFQzip_ext.py:19-21);
+    the device-side FASTQ parse / emit of the tools and their host-side fallbacks give identical files."""
+    _need_tools()
+    bases, quals, off = synth.make_reads(4000, 70, 5, var_len=True)
+    fq = tmp_path / "in.fastq"
+    fastq.write_fastq(str(fq), bases, quals, off)
+    outs = {}
+    for tag, env in (("dev", {}), ("host", {"BFQ_HOST_PARSE": "1", "BFQ_HOST_EMIT": "1"})):
+        out = str(tmp_path / tag)
+        e = dict(os.environ, **env)
+        subprocess.check_call(f"{BIN}/eGap {fq} --em --mem 1 --qs -o {out} --lcp --lbytes 1".split(), stdout=subprocess.DEVNULL, env=e)
+        subprocess.check_call(f"{BIN}/bfq_ext -e {out}.bwt -q {out}.bwt.qs -a {out}.1.lcp -o {out} -l 250 -s 0 -m 5".split(),
+                              stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, env=e)
+        outs[tag] = [open(out + ext, "rb").read() for ext in (".bwt", ".bwt.qs", ".1.lcp", ".fq")]
+    assert outs["dev"] == outs["host"]
+    out = str(tmp_path / "dev")
+    subprocess.check_call(f"{BIN}/bfq_ext -e {out}.bwt -q {out}.bwt.qs -a {out}.1.lcp -o {out} -l 250 -s 0 -m 5 -C".split(),
+                          stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    lines = open(out + ".fq", "rb").read().split(b"\n")
+    assert open(out + ".fq", "rb").read() == outs["dev"][3]
+    assert open(out + ".fq.dna", "rb").read() == b"".join(x + b"\n" for x in lines[1::4])
+    assert open(out + ".fq.qs", "rb").read() == b"".join(x + b"\n" for x in lines[3::4])

@@ -61,8 +61,9 @@ int main(int argc, char **argv)
     char default_value = '\0';
     float fthr = 0.0f;
     char TERM = '#';
+    bool components = false;
     int opt;
-    while ((opt = getopt(argc, argv, "he:q:o:a:l:k:m:v:f:t:s:T:H:G:DV")) != -1) {
+    while ((opt = getopt(argc, argv, "he:q:o:a:l:k:m:v:f:t:s:T:H:G:DVC")) != -1) {
         switch (opt) {
         case 'h': help(); break;
         case 'e': input_dna = optarg; break;
@@ -80,6 +81,7 @@ int main(int argc, char **argv)
         case 'G': device = atoi(optarg); break;
         case 'H': input_titles = optarg; headers = true; break;
         case 'D': case 'V': break;
+        case 'C': components = true; break;                     // extension: also write OUT.fq.dna / OUT.fq.qs (step 4's streams)
         default: help(); return -1;
         }
     }
@@ -123,10 +125,14 @@ int main(int argc, char **argv)
         for (uint64_t i = 0; i < n; i++) nreads += fb.data[i] == P.eos_byte;     // numSeq (bfq_ext.cpp:160-166)
         // Without a header file the records ("@" headers) are assembled on the device and arrive as the text of OUT.fq;
         // with -H the flat reads come back and the records are formatted here around the caller's header lines.
-        const bool device_emit = !headers && !getenv("BFQ_HOST_EMIT");
+        const bool device_emit = (!headers && !getenv("BFQ_HOST_EMIT")) || components;
+        if (components && headers) { std::cerr << "Error: -C (component streams) is not combined with -H" << endl; return EXIT_FAILURE; }
         const uint64_t text_cap = device_emit ? 2 * (n - nreads) + 6 * nreads + 64 : 1;
         const uint64_t flat_cap = device_emit ? 1 : (n ? n : 1);
         std::unique_ptr<uint8_t[]> text(new uint8_t[text_cap]), ob(new uint8_t[flat_cap]), oq(new uint8_t[flat_cap]);
+        const uint64_t comp_cap = components ? n + 1 : 1;
+        std::unique_ptr<uint8_t[]> dna(new uint8_t[comp_cap]), qsl(new uint8_t[comp_cap]);
+        memset(dna.get(), 0, comp_cap); memset(qsl.get(), 0, comp_cap);
         std::vector<uint64_t> off(device_emit ? 1 : nreads + 1);
         uint64_t text_size = 0;
         // touch the output pages now (the device is still coming up): a download into untouched memory faults page by page
@@ -137,7 +143,8 @@ int main(int argc, char **argv)
         if (std::get<0>(cr) != BFQ_OK) { std::cerr << "Error: " << std::get<2>(cr) << endl; return EXIT_FAILURE; }
         bfq_stats S;
         auto t1 = std::chrono::steady_clock::now();
-        int rc = device_emit ? bfq_smooth_rebuild_fastq(ctx, fb.data, fq.data, fl.data, n, &P, text.get(), text_cap, &text_size, &S)
+        int rc = device_emit ? bfq_smooth_rebuild_fastq(ctx, fb.data, fq.data, fl.data, n, &P, text.get(), text_cap, &text_size,
+                                                        components ? dna.get() : nullptr, components ? qsl.get() : nullptr, &S)
                              : bfq_smooth_rebuild(ctx, fb.data, fq.data, fl.data, n, &P, ob.get(), oq.get(), off.data(), nreads + 1, &S);
         if (rc != BFQ_OK) { std::cerr << "Error: " << bfq_last_error() << endl; bfq_ctx_destroy(ctx); return EXIT_FAILURE; }
         auto t2 = std::chrono::steady_clock::now();
@@ -166,6 +173,12 @@ int main(int argc, char **argv)
             }
         }
         if (fclose(fo) != 0) { std::cerr << "Error closing " << output << ".fq" << endl; return EXIT_FAILURE; }
+        if (components) {
+            // text = 2 T + 6 R bytes with 4 R newlines... the streams hold T + R bytes: (text_size - 6 R) / 2 + R, R = S.nreads
+            const uint64_t k = (text_size - 6 * S.nreads) / 2 + S.nreads;
+            bfqio::write_all(output + ".fq.dna", dna.get(), k);
+            bfqio::write_all(output + ".fq.qs", qsl.get(), k);
+        }
         auto t3 = std::chrono::steady_clock::now();
         std::cerr << "\nThe rebuilt file is ready!\n\n";
 
