@@ -245,10 +245,11 @@ def gpu_arm(args):
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         KNAME = {"radix_pass": "rs_onesweep_kernel", "radix_hist": "rs_hist_kernel", "pack": "pack_reads_kernel+pack3_kernel",
-                 "keys": "init_keys_kernel", "group": "group_tile_kernel", "defer": "defer_*_kernel", "hist": "hist256_kernel",
+                 "keys": "rs_suffix_keys_kernel", "group": "group_tile_kernel", "defer": "defer_*_kernel", "hist": "hist256_kernel",
                  "rank": "rank_*_kernel", "cluster": "cluster_tile_kernel", "cluster_long": "cluster_long_kernel",
                  "rule11": "rule11_kernel", "walk": "walk_kernel", "assemble": "assemble_kernel"}
-        TRAFFIC = {"group": 1782.1e6, "radix_pass": None}     # ncu dram read+write per launch (profiles/), where captured
+        # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1g_hot_kernels.txt), where captured
+        TRAFFIC = {"group": 1788.9e6, "radix_pass": 2437.5e6, "cluster": 425.7e6, "keys": 1393.8e6}
         roof_all = {}
         for k, (k_ms, k_n, k_bytes) in prof.items():
             if k_ms > 0 and k_n:
