@@ -335,15 +335,14 @@ __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stat
 }
 
 template <bool FLAT>
-__global__ void __launch_bounds__(CL_THREADS)
+__global__ void __launch_bounds__(CL_THREADS, 6)
 cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
                     uint8_t *__restrict__ obase, SmoothLists L)
 {
-    __shared__ uint8_t s_lcp[CL_S + 8];         // s_lcp[r + 1] = lcp[t0 + r], r = -1 .. CL_S + 1
-    __shared__ uint8_t s_code[CL_S];
-    __shared__ uint8_t s_q[CL_S];
-    __shared__ uint8_t s_f[CL_S + 4];           // rule 5-6 flag of every staged row (+ one past the window)
+    __shared__ __align__(16) uint8_t s_code[CL_S + 16];
+    __shared__ __align__(16) uint8_t s_q[CL_S + 16];
+    __shared__ __align__(16) uint8_t s_f[CL_S + 16];   // rule 5-6 flag of every staged row (+ one past the window)
     __shared__ uint16_t s_starts[CL_TILE / 2 + 2];
     __shared__ uint32_t s_nstarts, s_lead;
     __shared__ uint8_t s_lut[256];
@@ -356,23 +355,48 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     if (tid == 0) { s_nstarts = 0; s_lead = CL_TILE; }
     if (tid < ST_COUNT) s_stats[tid] = 0;
     __syncthreads();
-    for (int r = tid; r < CL_S + 3; r += CL_THREADS) {
-        int64_t i = t0 + r - 1;
-        s_lcp[r] = (i >= 0 && i < nn) ? lcp[i] : 0;
-    }
-    for (int r = tid; r < CL_S; r += CL_THREADS) {
-        int64_t i = t0 + r;
-        bool ok = i < nn;
-        s_code[r] = ok ? s_lut[bwt[i]] : 0;
-        s_q[r] = ok ? qs[i] : 0;
-    }
-    __syncthreads();
-    // flags of rows t0 .. t0 + CL_S (the last one only tells whether a cluster ends inside the window)
-    for (int r = tid; r <= CL_S; r += CL_THREADS) {
-        int64_t i = t0 + r;
-        bool f = false;
-        if (i > 0 && i < nn) f = f_flag(s_lcp[r], s_lcp[r + 1], s_lcp[r + 2], false, i == nn - 1);
-        s_f[r] = f;
+    // ---- staging, 16 rows per thread and step: codes, qualities and the rule 5-6 flags (3-point stencil on the LCP,
+    // computed in registers: the LCP itself is not kept).  Chunk CL_S / 16 only supplies the flag of row t0 + CL_S.
+    const bool vec = ((reinterpret_cast<uintptr_t>(bwt) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(lcp)) & 15) == 0;
+    for (int k = tid; k <= CL_S / 16; k += CL_THREADS) {
+        const int r0 = 16 * k;
+        const int64_t i0 = t0 + r0;
+        uint32_t wl[4] = {0, 0, 0, 0}, cw[4] = {0, 0, 0, 0}, qw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0};     // 16 packed bytes each
+        if (vec && i0 + 16 <= nn) {
+            const uint4 vl = *reinterpret_cast<const uint4 *>(lcp + i0);
+            const uint4 vb = *reinterpret_cast<const uint4 *>(bwt + i0);
+            const uint4 vq = *reinterpret_cast<const uint4 *>(qs + i0);
+            wl[0] = vl.x; wl[1] = vl.y; wl[2] = vl.z; wl[3] = vl.w;
+            qw[0] = vq.x; qw[1] = vq.y; qw[2] = vq.z; qw[3] = vq.w;
+            const uint32_t wb[4] = {vb.x, vb.y, vb.z, vb.w};
+#pragma unroll
+            for (int j = 0; j < 16; j++) cw[j >> 2] |= (uint32_t)s_lut[(wb[j >> 2] >> (8 * (j & 3))) & 255u] << (8 * (j & 3));
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                const int64_t i = i0 + j;
+                if (i < nn) {
+                    wl[j >> 2] |= (uint32_t)lcp[i] << (8 * (j & 3));
+                    cw[j >> 2] |= (uint32_t)s_lut[bwt[i]] << (8 * (j & 3));
+                    qw[j >> 2] |= (uint32_t)qs[i] << (8 * (j & 3));
+                }
+            }
+        }
+        const uint32_t lprev = (i0 > 0 && i0 - 1 < nn) ? lcp[i0 - 1] : 0u, lnext = (i0 + 16 < nn) ? lcp[i0 + 16] : 0u;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+            const int64_t i = i0 + j;
+            const uint32_t lm = j == 0 ? lprev : (wl[(j - 1) >> 2] >> (8 * ((j - 1) & 3))) & 255u;
+            const uint32_t l0 = (wl[j >> 2] >> (8 * (j & 3))) & 255u;
+            const uint32_t lp = j == 15 ? lnext : (wl[(j + 1) >> 2] >> (8 * ((j + 1) & 3))) & 255u;
+            const bool f = (i > 0 && i < nn) ? f_flag((int)lm, (int)l0, (int)lp, false, i == nn - 1) : false;
+            fw[j >> 2] |= (uint32_t)f << (8 * (j & 3));
+        }
+        *reinterpret_cast<uint4 *>(s_f + r0) = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+        if (r0 < CL_S) {
+            *reinterpret_cast<uint4 *>(s_code + r0) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+            *reinterpret_cast<uint4 *>(s_q + r0) = make_uint4(qw[0], qw[1], qw[2], qw[3]);
+        }
     }
     __syncthreads();
 
@@ -443,9 +467,27 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     __syncthreads();
     // ---- stored qualities of the rows this tile owns
     const uint32_t lead = s_lead;
-    for (int r = tid; r < CL_TILE; r += CL_THREADS) {
-        int64_t i = t0 + r;
-        if (i < nn && (uint32_t)r >= lead) *q_slot<FLAT>(lines, (uint64_t)i) = store_q(s_q[r]);
+    for (int k = tid; k < CL_TILE / 16; k += CL_THREADS) {
+        const int r0 = 16 * k;
+        const int64_t i0 = t0 + r0;
+        if (i0 >= nn || (uint32_t)(r0 + 15) < lead) continue;
+        uint8_t *dst = q_slot<FLAT>(lines, (uint64_t)i0);         // 16 rows = the quality half of one walk sector
+        if ((uint32_t)r0 >= lead && i0 + 16 <= nn && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(s_q + r0);
+            uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#if BFQ_B
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const uint32_t x = w[j];
+                w[j] = (uint32_t)store_q((uint8_t)x) | ((uint32_t)store_q((uint8_t)(x >> 8)) << 8) |
+                       ((uint32_t)store_q((uint8_t)(x >> 16)) << 16) | ((uint32_t)store_q((uint8_t)(x >> 24)) << 24);
+            }
+#endif
+            *reinterpret_cast<uint4 *>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else {
+            for (int j = 0; j < 16; j++)
+                if (i0 + j < nn && (uint32_t)(r0 + j) >= lead) *q_slot<FLAT>(lines, (uint64_t)(i0 + j)) = store_q(s_q[r0 + j]);
+        }
     }
     flush_stats(st, s_stats, L.stats);
 }
