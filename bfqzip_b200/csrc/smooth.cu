@@ -401,11 +401,22 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     __syncthreads();
 
     // ---- cluster starts and the leading run
-    for (int r = tid; r < CL_TILE; r += CL_THREADS) {
-        if (t0 + r >= nn) break;
-        if (!s_f[r]) {
-            atomicMin(&s_lead, (uint32_t)r);
-            if (s_f[r + 1]) s_starts[atomicAdd(&s_nstarts, 1u)] = (uint16_t)r;
+    for (int k = tid; k < CL_TILE / 16; k += CL_THREADS) {
+        const int r0 = 16 * k;
+        if (t0 + r0 >= nn) break;
+        const uint4 v = *reinterpret_cast<const uint4 *>(s_f + r0);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint32_t m = (uint32_t)s_f[r0 + 16] << 16;                 // bit j = flag of row r0 + j
+#pragma unroll
+        for (int j = 0; j < 16; j++) m |= ((w[j >> 2] >> (8 * (j & 3))) & 1u) << j;
+        const int64_t left = nn - (t0 + r0);
+        const uint32_t notf = ~m & (left >= 16 ? 0xFFFFu : ((1u << left) - 1u));
+        if (notf) atomicMin(&s_lead, (uint32_t)(r0 + __ffs(notf) - 1));
+        uint32_t starts = notf & (m >> 1);                         // an unflagged row followed by a flagged one opens a cluster
+        while (starts) {
+            const int j = __ffs(starts) - 1;
+            s_starts[atomicAdd(&s_nstarts, 1u)] = (uint16_t)(r0 + j);
+            starts &= starts - 1;
         }
     }
     __syncthreads();
