@@ -307,6 +307,8 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
                                  uint64_t *n_local, uint64_t *row_base, uint64_t *prev_key, bool *has_prev);
 // Sorts (key, 16-bit payload) pairs whose keys are exactly the integers 0..n-1 in some order (applying a
 // permutation with streaming passes instead of a random scatter); the digit histograms are computed on the host.
+// Only the VALUES come out in key order (vals_a when the returned flag is 0, vals_b when 1): the passes cover the high key bits
+// and a placement pass in shared memory finishes the low 15 (a bucket of a permutation sits exactly where it belongs).
 int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n);
 // Level-0 keys of the suffix sort: k symbols of every text position (cut at the terminator, QL[p] in the
 // unsorted bits 63..48 when given) with payload = position, built and histogrammed in one kernel, then sorted

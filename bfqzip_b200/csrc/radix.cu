@@ -572,21 +572,59 @@ static uint32_t count_digit(uint64_t n, int shift, int bits, uint32_t d)
     return (uint32_t)c;
 }
 
+// Last step of the permutation sort: after the passes on the high key bits, bucket b = keys [b << PL_BITS, (b + 1) << PL_BITS)
+// sits exactly at elements [b << PL_BITS, ...) -- the keys are a permutation of 0..n-1 -- so one block puts every value of a
+// bucket at smem[key & mask] and writes the bucket out in order.  No ranking, no key output: a pure stream.
+constexpr int PL_BITS = 15;
+constexpr int PL_THREADS = 512;
+__global__ void __launch_bounds__(PL_THREADS)
+rs_place_kernel(const uint32_t *__restrict__ keys, const uint16_t *__restrict__ vals, uint32_t n, uint16_t *__restrict__ out)
+{
+    extern __shared__ __align__(16) uint16_t pl_smem[];
+    const uint32_t base = blockIdx.x << PL_BITS;
+    const uint32_t cnt = min(1u << PL_BITS, n - base);
+    for (uint32_t i = threadIdx.x; i < cnt; i += PL_THREADS)
+        pl_smem[__ldcs(keys + base + i) & ((1u << PL_BITS) - 1u)] = __ldcs(vals + base + i);
+    __syncthreads();
+    if (cnt == (1u << PL_BITS)) {
+        const uint4 *s = reinterpret_cast<const uint4 *>(pl_smem);
+        uint4 *o = reinterpret_cast<uint4 *>(out + base);                       // base * 2 bytes is a multiple of 16
+        for (uint32_t i = threadIdx.x; i < (1u << PL_BITS) / 8; i += PL_THREADS) __stcs(o + i, s[i]);
+    } else {
+        for (uint32_t i = threadIdx.x; i < cnt; i += PL_THREADS) out[base + i] = pl_smem[i];
+    }
+}
+
 int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n)
 {
     if (n == 0) return 0;
     if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
     int bits = 1;
     while (((uint64_t)1 << bits) < n) bits++;
-    RsPasses P = plan_passes(bits);
+    const bool aligned = ((reinterpret_cast<uintptr_t>(vals_a) | reinterpret_cast<uintptr_t>(vals_b)) & 15) == 0;
+    const int low = aligned ? std::min(bits, PL_BITS) : 0;          // bits finished by the placement pass
+    RsPasses P = plan_passes(bits - low);
+    for (int p = 0; p < P.num; p++) P.shift[p] += low;
     Arena::Mark mk = c->arena.mark();
-    uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
-    std::vector<uint32_t> h(RS_MAX_PASSES * RS_RADIX, 0);
-    for (int p = 0; p < P.num; p++)
-        for (uint32_t d = 0; d < (1u << P.bits[p]); d++) h[p * RS_RADIX + d] = count_digit(n, P.shift[p], P.bits[p], d);
-    // pageable source: the copy is staged by the runtime before the call returns
-    BFQ_CUDA(cudaMemcpyAsync(hist, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-    const int flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
+    int flip = 0;
+    if (P.num) {
+        uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
+        std::vector<uint32_t> h(RS_MAX_PASSES * RS_RADIX, 0);
+        for (int p = 0; p < P.num; p++)
+            for (uint32_t d = 0; d < (1u << P.bits[p]); d++) h[p * RS_RADIX + d] = count_digit(n, P.shift[p], P.bits[p], d);
+        // pageable source: the copy is staged by the runtime before the call returns
+        BFQ_CUDA(cudaMemcpyAsync(hist, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+        flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
+    }
+    if (low) {
+        const size_t smem = sizeof(uint16_t) << PL_BITS;
+        BFQ_CUDA(cudaFuncSetAttribute(rs_place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ProfScope ps(c, PC_RADIX_PASS, n * (4 + 2 + 2));
+        rs_place_kernel<<<div_up(n, (uint64_t)1 << PL_BITS), PL_THREADS, smem, c->stream>>>(
+            flip ? keys_b : keys_a, flip ? vals_b : vals_a, (uint32_t)n, flip ? vals_a : vals_b);
+        BFQ_CUDA(cudaGetLastError());
+        flip ^= 1;                                                  // only the values are in order now (the keys are known: 0..n-1)
+    }
     c->arena.release(mk);
     return flip;
 }
