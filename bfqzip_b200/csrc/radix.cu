@@ -138,6 +138,18 @@ template <typename S> __device__ __forceinline__ void st_status(S *p, S v)
     *((volatile S *)p) = v;
 }
 
+// m &= lanes whose digit has the same bit B.  Four instructions (test with predicate output, vote, conditional
+// complement, and); the C form compiles to six or seven per bit.
+template <int B> __device__ __forceinline__ void match_bit(uint32_t d, uint32_t &m)
+{
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b32 t, v;\n\t"
+                 "setp.ne.u32 q, 0, 0;\n\t"
+                 "lop3.or.b32 t|p, %1, %2, 0, 0xC0, q;\n\t"
+                 "vote.sync.ballot.b32 v, p, 0xffffffff;\n\t"
+                 "@!p not.b32 v, v;\n\tand.b32 %0, %0, v;\n\t}"
+                 : "+r"(m) : "r"(d), "n"(1u << B));
+}
+
 template <typename K, typename V, typename S, int ITEMS>
 __global__ void __launch_bounds__(RS_THREADS, 4)
 rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
@@ -183,11 +195,10 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     for (int i = 0; i < ITEMS; i++) {
         uint32_t d = digit_of(key[i], shift, mask);
         // lanes with the same digit: one ballot per digit bit (match.any is far slower with ~30 distinct values per warp)
+        // (always all 8 digit bits: a pass with fewer bits has zeros above them, which match everywhere)
         uint32_t m = 0xffffffffu;
-        for (int b = 0; b < bits; b++) {
-            const uint32_t vote = __ballot_sync(0xffffffffu, (d >> b) & 1u);
-            m &= ((d >> b) & 1u) ? vote : ~vote;
-        }
+        match_bit<0>(d, m); match_bit<1>(d, m); match_bit<2>(d, m); match_bit<3>(d, m);
+        match_bit<4>(d, m); match_bit<5>(d, m); match_bit<6>(d, m); match_bit<7>(d, m);
         uint32_t prev = warp_cnt[w][d];
         __syncwarp();
         if ((__ffs(m) - 1) == lane) warp_cnt[w][d] = prev + __popc(m);
@@ -238,6 +249,14 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
         stage[p] = key[i];
     }
 
+    // the payload loads are issued here: they are in flight during the chained scan and the key output
+    V val[ITEMS];
+#pragma unroll
+    for (int i = 0; i < ITEMS; i++) {
+        uint32_t loc = wbase + i * 32;
+        val[i] = (loc < valid) ? vals_in[tile_base + loc] : (V)0;
+    }
+
     // ---- chained scan: exclusive prefix of this digit over all earlier tiles
     {
         uint32_t excl = 0;
@@ -271,11 +290,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     // ---- payload through the same permutation
     V *stage32 = reinterpret_cast<V *>(stage);
 #pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        uint32_t loc = wbase + i * 32;
-        V v = (loc < valid) ? vals_in[tile_base + loc] : (V)0;
-        stage32[lpos[i]] = v;
-    }
+    for (int i = 0; i < ITEMS; i++) stage32[lpos[i]] = val[i];
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
