@@ -168,7 +168,6 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     __shared__ uint32_t digit_gbase[RS_RADIX];
     __shared__ uint32_t warp_tot[RS_WARPS];
     __shared__ K stage[TILE];
-    __shared__ uint8_t s_dig[TILE];              // digit of the key staged at each slot (for the payload pass)
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t mask = (1u << bits) - 1;
@@ -276,14 +275,14 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     }
     __syncthreads();
 
-    // ---- coalesced output of keys; keep each slot's digit for the payload pass
+    // ---- coalesced output of keys; the destination of each slot stays in registers for the payload pass
+    uint32_t dst[ITEMS];
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t slot = i * RS_THREADS + tid;
         K k = stage[slot];
-        uint32_t d = digit_of(k, shift, mask);
-        s_dig[slot] = (uint8_t)d;
-        if (slot < valid) keys_out[digit_gbase[d] + slot] = k;
+        dst[i] = digit_gbase[digit_of(k, shift, mask)] + slot;
+        if (slot < valid) keys_out[dst[i]] = k;
     }
     __syncthreads();
 
@@ -295,7 +294,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t slot = i * RS_THREADS + tid;
-        if (slot < valid) vals_out[digit_gbase[s_dig[slot]] + slot] = stage32[slot];
+        if (slot < valid) vals_out[dst[i]] = stage32[slot];
     }
 }
 

@@ -151,6 +151,7 @@ constexpr int GT_E = 256;
 constexpr int GT_S = GT_T + GT_E;
 constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
 constexpr int GT_GMAX = GT_S / 2;
+constexpr int GT_RW = 13;                             // words of 21 symbols that hold the longest suffix tail (255 symbols)
 
 template <typename P>
 struct GroupTileArgsT {
@@ -177,6 +178,7 @@ struct GroupTileArgsT {
     uint64_t kmask;             // key bits that take part in group equality (level 0: the 3*ksym symbol bits)
     int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
+    int dbg;
 };
 using GroupTileArgs = GroupTileArgsT<uint32_t>;
 
@@ -220,20 +222,59 @@ __device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, c
 {
     // The strings are read straight from the packed text (L1 / pinned L2): a member is compared once per
     // iteration, so staging it in shared memory would cost more than it saves (and occupancy with it).
-    const uint32_t lm = s_len[mem], lr = s_len[ref];
-    const uint32_t lmin = min(lm, lr);
+    const uint32_t lm = s_len[mem], lr = s_len[ref];      // the reference is its run's longest member: lm <= lr
     const uint64_t pm = (uint64_t)s_pos[mem] + depth, pr = (uint64_t)s_pos[ref] + depth;
     RefCmp o;
-    o.l = lmin;
+    o.l = lm; o.c = 0u;
     if (mem != ref) {
-        const uint32_t jend = (lmin + 20u) / 21u;         // a difference cannot lie past the shorter string's terminator
+        const uint32_t jend = (lm + 20u) / 21u;           // a difference cannot lie past the member's terminator
         for (uint32_t j = D / 21u; j < jend; j++) {
-            const uint64_t x = text_window(T3, pm + 21u * j) ^ text_window(T3, pr + 21u * j);
-            if (x) { o.l = min(lmin, 21u * j + (uint32_t)(__clzll((long long)x) / 3)); break; }
+            const uint64_t wm = text_window(T3, pm + 21u * j), wr = text_window(T3, pr + 21u * j);
+            const uint64_t x = wm ^ wr;
+            if (x) {
+                const uint32_t f = (uint32_t)(__clzll((long long)x) / 3);
+                if (21u * j + f < lm) {                   // both symbols at the difference come from the two windows
+                    o.l = 21u * j + f;
+                    o.c = (uint32_t)((wm << (3u * f)) >> 61);
+                    o.r = (uint32_t)((wr << (3u * f)) >> 61);
+                    return o;
+                }
+                break;
+            }
         }
     }
-    o.c = o.l < lm ? sym_code(T3, pm + o.l) : 0u;
-    o.r = o.l < lr ? sym_code(T3, pr + o.l) : 0u;
+    // the member is a prefix of the reference (or the reference itself): c = its terminator
+    o.r = lm < lr ? sym_code(T3, pr + lm) : 0u;
+    return o;
+}
+
+// First iteration of a group: every member is compared with the same string V, whose words the warp keeps in shared
+// memory.  ANY fixed string orders the members correctly (the (type, l, c) classes and the min(l, l') LCP rule only need
+// "the same string for everybody"), so V is the group's longest member a corrected by a per-symbol majority vote with
+// the second and third longest members b and c wherever all three reach: one sequencing error in a -- more than half of
+// the longest reads of a 100 bp collection have one -- would otherwise make every longer member tie at that symbol and
+// cost the whole group another iteration.
+__device__ __forceinline__ RefCmp v_compare(const uint64_t *__restrict__ T3, const uint64_t *s_v, uint64_t pm, uint32_t lm)
+{
+    RefCmp o;
+    o.l = lm; o.c = 0u;
+    const uint32_t jend = (lm + 20u) / 21u;
+    for (uint32_t j = 0; j < jend; j++) {
+        const uint64_t wm = text_window(T3, pm + 21u * j), wr = s_v[j];
+        const uint64_t x = wm ^ wr;
+        if (x) {
+            const uint32_t f = (uint32_t)(__clzll((long long)x) / 3);
+            if (21u * j + f < lm) {
+                o.l = 21u * j + f;
+                o.c = (uint32_t)((wm << (3u * f)) >> 61);
+                o.r = (uint32_t)((wr << (3u * f)) >> 61);
+                return o;
+            }
+            break;
+        }
+    }
+    const uint32_t j = lm / 21u, f = lm - 21u * j;        // V's symbol after the member's last one (0 = a's terminator)
+    o.r = (uint32_t)((s_v[j] << (3u * f)) >> 61);
     return o;
 }
 
@@ -254,7 +295,7 @@ __device__ __forceinline__ uint32_t class_l(uint32_t cls)
 template <int R, typename P>
 __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
                                                  const P *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
-                                                 uint8_t *s_lcpout)
+                                                 uint8_t *s_lcpout, uint64_t *s_refw, int dbg)
 {
     constexpr uint32_t IB = 6, IM = 63u;                  // position index bits
     uint32_t key[R], runa[R], rdepth[R];
@@ -265,16 +306,49 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
         runa[s] = 0;
         rdepth[s] = t < len ? 0u : 0xFFu;
     }
-    if (lane == 0) s_best[gs] = 0;
-    __syncwarp();
-    while (true) {
+    {   // V: the three longest members (valid bit | length | row), then lane j builds word j
+        uint32_t v[R], a = 0, b = 0, cc = 0;
 #pragma unroll
-        for (int s = 0; s < R; s++)
-            if (rdepth[s] != 0xFFu) {
-                const uint32_t mem = gs + (key[s] & IM);
-                atomicMax(&s_best[gs + runa[s]], ((uint32_t)s_len[mem] << 16) | mem);
+        for (int s = 0; s < R; s++) {
+            const uint32_t t = s * 32 + lane;
+            v[s] = t < len ? (0x80000000u | ((uint32_t)s_len[gs + t] << 16) | t) : 0u;
+            a = max(a, v[s]);
+        }
+        a = __reduce_max_sync(0xffffffffu, a);
+#pragma unroll
+        for (int s = 0; s < R; s++) if (v[s] != a) b = max(b, v[s]);
+        b = __reduce_max_sync(0xffffffffu, b);
+#pragma unroll
+        for (int s = 0; s < R; s++) if (v[s] != a && v[s] != b) cc = max(cc, v[s]);
+        cc = __reduce_max_sync(0xffffffffu, cc);
+        const uint32_t la = (a >> 16) & 255u, lc = (cc >> 16) & 255u;
+        const uint32_t nw = la / 21u + 1u;                // the word that holds a's terminator included
+        if ((uint32_t)lane < nw) {
+            const uint32_t j = lane;
+            uint64_t w = text_window(T3, (uint64_t)s_pos[gs + (a & 0xFFFFu)] + depth + 21u * j);
+            if (cc && lc > 21u * j) {                     // symbols of this word that all three members reach
+                const uint32_t cnt = min(21u, lc - 21u * j);
+                const uint64_t vote = ~0ull << (64 - 3 * cnt);
+                const uint64_t wb = text_window(T3, (uint64_t)s_pos[gs + (b & 0xFFFFu)] + depth + 21u * j);
+                const uint64_t wc = text_window(T3, (uint64_t)s_pos[gs + (cc & 0xFFFFu)] + depth + 21u * j);
+                const uint64_t maj = (w & wb) | (w & wc) | (wb & wc);          // per symbol: the value two of them share
+                w = (maj & vote) | (w & ~vote);
             }
+            s_refw[j] = w;
+        }
         __syncwarp();
+    }
+    bool first = true;
+    while (true) {
+        if (!first) {
+#pragma unroll
+            for (int s = 0; s < R; s++)
+                if (rdepth[s] != 0xFFu) {
+                    const uint32_t mem = gs + (key[s] & IM);
+                    atomicMax(&s_best[gs + runa[s]], ((uint32_t)s_len[mem] << 16) | mem);
+                }
+            __syncwarp();
+        }
 #pragma unroll
         for (int s = 0; s < R; s++) {
             const uint32_t t = s * 32 + lane;
@@ -282,15 +356,17 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
                 const uint32_t idx = key[s] & IM;
                 if (rdepth[s] == 0xFFu) key[s] = (t << (13 + IB)) | idx;
                 else {
-                    const RefCmp o = ref_compare(T3, s_pos, s_len, depth, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
+                    const RefCmp o = first ? v_compare(T3, s_refw, (uint64_t)s_pos[gs + idx] + depth, s_len[gs + idx])
+                                           : ref_compare(T3, s_pos, s_len, depth, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
                     key[s] = (runa[s] << (13 + IB)) | (class_of(o) << IB) | idx;
                 }
             }
         }
+        first = false;
         // bitonic network, ascending comparators only (rows >= len hold +inf and never move)
 #pragma unroll
         for (uint32_t k = 2; k <= 32u * R; k <<= 1) {
-            if ((k >> 1) >= len) break;
+            if ((k >> 1) >= len || (dbg & 4)) break;
             const uint32_t half = k >> 1;
             if (k <= 32) {
 #pragma unroll
@@ -359,7 +435,7 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
             }
         }
         __syncwarp();
-        if (!__any_sync(0xffffffffu, any)) break;
+        if (!__any_sync(0xffffffffu, any) || (dbg & 8)) break;
     }
 #pragma unroll
     for (int s = 0; s < R; s++) {
@@ -475,6 +551,8 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     uint8_t *s_len = reinterpret_cast<uint8_t *>(s_glen + GT_GMAX);                 // [GT_S] staged symbols before the terminator
     uint8_t *s_rdepth = s_len + GT_S;                                               // [GT_S] depth of the row's run, 0xFF = resolved
     uint8_t *s_lcpout = s_rdepth + GT_S;                                            // [GT_S] LCP with the previous sorted row (staged part)
+    uint64_t *s_refw = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(s_lcpout + GT_S) + 7) & ~(uintptr_t)7) +
+                       (threadIdx.x >> 5) * GT_RW;                                  // [warps][GT_RW] words of the group's reference
     __shared__ uint32_t s_ngroups, s_next;
 
     const int tid = threadIdx.x, lane = tid & 31;
@@ -571,20 +649,21 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     __syncthreads();
 
     // ---- phase 2: one warp orders one group
-    const uint32_t ngroups = s_ngroups;
+    const uint32_t ngroups = (A.dbg & 1) ? 0u : s_ngroups;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&s_next, 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
         const uint32_t gs = s_gstart[g], len = s_glen[g];
-        if (len <= 32) order_group_regs<1, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
-        else if (len <= 64) order_group_regs<2, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout);
+        if (len <= 32) order_group_regs<1, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, A.dbg);
+        else if (len <= 64) order_group_regs<2, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, A.dbg);
         else order_group_smem<P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
         __syncwarp();
     }
     __syncthreads();
 
+    if (A.dbg & 2) return;
     // ---- phase 3: finished rows leave the SM in slot order
     for (int r = tid; r < GT_S; r += GT_THREADS) {
         const uint32_t gs = s_gs[r];
@@ -606,7 +685,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 static size_t group_tile_smem(size_t pos_bytes)
 {
     return (size_t)GT_S * 8 + (size_t)GT_S * (4 + pos_bytes) + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
-           (size_t)GT_S * 3 + 16;
+           (size_t)GT_S * 3 + (size_t)(GT_THREADS / 32) * GT_RW * 8 + 8 + 16;
 }
 
 // ============================================================================ deferred groups
@@ -858,6 +937,7 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
     G.T3 = T3; G.QL = QL; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
     G.group_cap = (uint32_t)c->opt_group_cap;
+    G.dbg = getenv("BFQ_DBG_GROUP") ? atoi(getenv("BFQ_DBG_GROUP")) : 0;
     G.prev_key = prev_key; G.has_prev = has_prev;
 
     int parity = 0, depth = 0, ksym = k, level = 0;
