@@ -539,7 +539,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
     uint64_t *s_key = reinterpret_cast<uint64_t *>(gt_smem);                        // [GT_S] keys of groups > 64 rows
-    P *s_pos = reinterpret_cast<P *>(s_key + GT_S);                                 // [GT_S] text position of the row's suffix
+    P *s_pos = reinterpret_cast<P *>(s_key + GT_S + 2);                                 // [GT_S] text position of the row's suffix
     uint32_t *s_best = reinterpret_cast<uint32_t *>(s_pos + GT_S);                                                // [GT_S] (length << 16 | row) of a run's reference
     uint32_t *s_head = s_best + GT_S;                                               // [GT_HW]
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] previous symbol code | its quality << 8
@@ -563,13 +563,30 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     const int kshift = 3 * ksym;                          // group id sits above the symbols (level >= 1)
     if (tid == 0) { s_ngroups = 0; s_next = 0; }
 
-    // ---- phase 0: head bitmap of the staged window (bit r <=> list slot t0 + r starts a group)
+    // ---- phase 0: the window's keys and positions come in with one batch of independent loads per thread (slot r of
+    // the window sits at s_key[r + 1]; [0] is the key before the window, [GT_S + 1] the one after it), then the head
+    // bitmap: bit r <=> list slot t0 + r starts a group
+    {
+        constexpr int NB = GT_S / GT_THREADS;
+        K kk[NB]; P pp[NB];
+#pragma unroll
+        for (int i = 0; i < NB; i++) {
+            const uint64_t j = (uint64_t)t0 + i * GT_THREADS + tid;
+            kk[i] = j < m ? __ldcs(&keys[j]) : (K)0;
+            pp[i] = j < m ? __ldcs(&A.pos[j]) : (P)0;
+        }
+        if (tid == 0) s_key[0] = t0 > 0 ? keys[t0 - 1] : (K)0;
+        if (tid == 32) s_key[GT_S + 1] = (uint64_t)t0 + GT_S < m ? keys[(uint64_t)t0 + GT_S] : (K)0;
+#pragma unroll
+        for (int i = 0; i < NB; i++) { s_key[i * GT_THREADS + tid + 1] = kk[i]; s_pos[i * GT_THREADS + tid] = pp[i]; }
+    }
+    __syncthreads();
     for (int base = 0; base < GT_HW * 32; base += GT_THREADS) {
         const int r = base + tid;
         const uint64_t j = (uint64_t)t0 + r;
         bool h = true;                                    // slots past the list end count as heads
         if (r <= GT_S && j < m && j > 0) {
-            const K kc = __ldcs(&keys[j]) & (K)A.kmask, kp = __ldcs(&keys[j - 1]) & (K)A.kmask;
+            const K kc = s_key[r + 1] & (K)A.kmask, kp = s_key[r] & (K)A.kmask;
             h = (kc != kp) || ((kc & (K)7) == 0);
         }
         const uint32_t bits = __ballot_sync(0xffffffffu, h);
@@ -611,10 +628,10 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
                         bool write = true; uint32_t l = 0;
                         if (j == 0) {
                             write = A.level0;
-                            if (A.level0 && A.has_prev) l = head_lcp<K>((K)A.prev_key, keys[0] & (K)A.kmask, ksym);
+                            if (A.level0 && A.has_prev) l = head_lcp<K>((K)A.prev_key, s_key[1] & (K)A.kmask, ksym);
                         }
                         else {
-                            const K kc = keys[j] & (K)A.kmask, kp = keys[j - 1] & (K)A.kmask;
+                            const K kc = s_key[r + 1] & (K)A.kmask, kp = s_key[r] & (K)A.kmask;
                             if (!A.level0 && ((uint64_t)kc >> kshift) != ((uint64_t)kp >> kshift)) write = false;   // written one level up
                             else l = A.depth0 + head_lcp<K>(kp, kc, ksym);
                         }
@@ -632,14 +649,13 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
                 }
                 if (fits) {
                     gs16 = (uint16_t)gs;
-                    const P p = __ldcs(&A.pos[j]);
+                    const P p = s_pos[r];
                     s_sorted[r] = (uint16_t)r;
-                    const uint32_t ql = A.embed ? (uint32_t)((uint64_t)keys[j] >> 48) : (uint32_t)A.QL[p];
+                    const uint32_t ql = A.embed ? (uint32_t)((uint64_t)s_key[r + 1] >> 48) : (uint32_t)A.QL[p];
                     if (A.bwt) {
                         const uint32_t c = p > 0 ? sym_code(A.T3, (uint64_t)p - 1) : 0u;
                         s_prev[r] = (uint16_t)(c | ((c ? (ql & 255u) : (uint32_t)A.eos) << 8));
                     }
-                    s_pos[r] = p;
                     s_len[r] = (uint8_t)max(0, (int)(ql >> 8) - depth);   // symbols of this suffix past the shared prefix
                 }
             }
@@ -684,7 +700,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 
 static size_t group_tile_smem(size_t pos_bytes)
 {
-    return (size_t)GT_S * 8 + (size_t)GT_S * (4 + pos_bytes) + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
+    return (size_t)(GT_S + 2) * 8 + (size_t)GT_S * (4 + pos_bytes) + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
            (size_t)GT_S * 3 + (size_t)(GT_THREADS / 32) * GT_RW * 8 + 8 + 16;
 }
 
