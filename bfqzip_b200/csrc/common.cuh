@@ -122,7 +122,12 @@ __device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
 
 __device__ __forceinline__ uint32_t sym_code(const uint64_t *__restrict__ T3, uint64_t p)
 {
-    return (uint32_t)(text_window(T3, p) >> 61);
+    const uint64_t bit = 3 * p;
+    const uint64_t wi = bit >> 6;
+    const int s = (int)(bit & 63);
+    const uint64_t w0 = T3[wi];
+    if (s <= 61) return (uint32_t)(w0 >> (61 - s)) & 7u;              // the symbol lies inside one word
+    return (uint32_t)(((w0 << s) | (T3[wi + 1] >> (64 - s))) >> 61);
 }
 #endif
 

@@ -178,7 +178,6 @@ struct GroupTileArgsT {
     uint64_t kmask;             // key bits that take part in group equality (level 0: the 3*ksym symbol bits)
     int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
-    int dbg;
 };
 using GroupTileArgs = GroupTileArgsT<uint32_t>;
 
@@ -295,7 +294,7 @@ __device__ __forceinline__ uint32_t class_l(uint32_t cls)
 template <int R, typename P>
 __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
                                                  const P *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
-                                                 uint8_t *s_lcpout, uint64_t *s_refw, int dbg)
+                                                 uint8_t *s_lcpout, uint64_t *s_refw)
 {
     constexpr uint32_t IB = 6, IM = 63u;                  // position index bits
     uint32_t key[R], runa[R], rdepth[R];
@@ -366,7 +365,7 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
         // bitonic network, ascending comparators only (rows >= len hold +inf and never move)
 #pragma unroll
         for (uint32_t k = 2; k <= 32u * R; k <<= 1) {
-            if ((k >> 1) >= len || (dbg & 4)) break;
+            if ((k >> 1) >= len) break;
             const uint32_t half = k >> 1;
             if (k <= 32) {
 #pragma unroll
@@ -435,7 +434,7 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
             }
         }
         __syncwarp();
-        if (!__any_sync(0xffffffffu, any) || (dbg & 8)) break;
+        if (!__any_sync(0xffffffffu, any)) break;
     }
 #pragma unroll
     for (int s = 0; s < R; s++) {
@@ -665,21 +664,20 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     __syncthreads();
 
     // ---- phase 2: one warp orders one group
-    const uint32_t ngroups = (A.dbg & 1) ? 0u : s_ngroups;
+    const uint32_t ngroups = s_ngroups;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&s_next, 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
         const uint32_t gs = s_gstart[g], len = s_glen[g];
-        if (len <= 32) order_group_regs<1, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, A.dbg);
-        else if (len <= 64) order_group_regs<2, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, A.dbg);
+        if (len <= 32) order_group_regs<1, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw);
+        else if (len <= 64) order_group_regs<2, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw);
         else order_group_smem<P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
         __syncwarp();
     }
     __syncthreads();
 
-    if (A.dbg & 2) return;
     // ---- phase 3: finished rows leave the SM in slot order
     for (int r = tid; r < GT_S; r += GT_THREADS) {
         const uint32_t gs = s_gs[r];
@@ -953,7 +951,6 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
     G.T3 = T3; G.QL = QL; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
     G.group_cap = (uint32_t)c->opt_group_cap;
-    G.dbg = getenv("BFQ_DBG_GROUP") ? atoi(getenv("BFQ_DBG_GROUP")) : 0;
     G.prev_key = prev_key; G.has_prev = has_prev;
 
     int parity = 0, depth = 0, ksym = k, level = 0;
