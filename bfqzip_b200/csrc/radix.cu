@@ -18,8 +18,9 @@ constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_RADIX = 256;
 constexpr int RS_MAX_PASSES = 8;
-#ifndef RS_PREFETCH_TILES
-#define RS_PREFETCH_TILES 592                          // 148 SMs x 4 resident CTAs
+#define RS_BLOCKS_PER_SM(items) ((items) >= 22 ? 3 : (items) >= 16 ? 4 : (items) >= 12 ? 5 : 6)
+#ifndef RS_ITEMS_MAIN
+#define RS_ITEMS_MAIN 16
 #endif
 
 struct RsPasses {
@@ -154,7 +155,7 @@ template <int B> __device__ __forceinline__ void match_bit(uint32_t d, uint32_t 
 }
 
 template <typename K, typename V, typename S, int ITEMS>
-__global__ void __launch_bounds__(RS_THREADS, 4)
+__global__ void __launch_bounds__(RS_THREADS, RS_BLOCKS_PER_SM(ITEMS))
 rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
                    const V *__restrict__ vals_in, V *__restrict__ vals_out,
                    uint32_t n, int shift, int bits, const uint32_t *__restrict__ digit_base,
@@ -170,7 +171,8 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     __shared__ uint32_t digit_start[RS_RADIX];
     __shared__ uint32_t digit_gbase[RS_RADIX];
     __shared__ uint32_t warp_tot[RS_WARPS];
-    __shared__ K stage[TILE];
+    extern __shared__ __align__(16) unsigned char rs_stage[];     // TILE keys (dynamic: more than 48 KiB for the larger tiles)
+    K *stage = reinterpret_cast<K *>(rs_stage);
 
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t mask = (1u << bits) - 1;
@@ -186,7 +188,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     // ---- the tile that starts when this one ends (about one wave of resident CTAs later) is pulled into L2 now, so the
     // loads at the top of a CTA see L2 latency instead of DRAM latency
     {
-        const uint64_t ahead = ((uint64_t)tile + RS_PREFETCH_TILES) * TILE;
+        const uint64_t ahead = ((uint64_t)tile + 148u * RS_BLOCKS_PER_SM(ITEMS)) * TILE;
         if (ahead < n) {
             const char *kp = reinterpret_cast<const char *>(keys_in + ahead);
             const char *vp = reinterpret_cast<const char *>(vals_in + ahead);
@@ -331,16 +333,21 @@ static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, 
     }
     K *kin = keys_a, *kout = keys_b;
     V *vin = vals_a, *vout = vals_b;
+    if ((size_t)TILE * sizeof(K) > 32 * 1024) {
+        BFQ_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<K, V, uint64_t, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TILE * sizeof(K))));
+        BFQ_CUDA(cudaFuncSetAttribute(rs_onesweep_kernel<K, V, uint32_t, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(TILE * sizeof(K))));
+    }
     for (int p = 0; p < P.num; p++) {
         BFQ_CUDA(cudaMemsetAsync(status, 0, status_bytes, c->stream));
         {
             ProfScope ps(c, PC_RADIX_PASS, 2 * n * (sizeof(K) + sizeof(V)));
+            const size_t dyn = (size_t)TILE * sizeof(K);
             if (wide)
-                rs_onesweep_kernel<K, V, uint64_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
+                rs_onesweep_kernel<K, V, uint64_t, ITEMS><<<tiles, RS_THREADS, dyn, c->stream>>>(
                     kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
                     (uint64_t *)status, tile_counter);
             else
-                rs_onesweep_kernel<K, V, uint32_t, ITEMS><<<tiles, RS_THREADS, 0, c->stream>>>(
+                rs_onesweep_kernel<K, V, uint32_t, ITEMS><<<tiles, RS_THREADS, dyn, c->stream>>>(
                     kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
                     (uint32_t *)status, tile_counter);
         }
@@ -585,7 +592,7 @@ int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, u
         rs_suffix_keys_kernel<<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
         BFQ_CUDA(cudaGetLastError());
     }
-    const int flip = radix_passes<uint64_t, uint32_t, 16>(c, keys_a, keys_b, pos_a, pos_b, n, P, hist);
+    const int flip = radix_passes<uint64_t, uint32_t, RS_ITEMS_MAIN>(c, keys_a, keys_b, pos_a, pos_b, n, P, hist);
     c->arena.release(mk);
     return flip;
 }
