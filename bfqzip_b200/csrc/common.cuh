@@ -212,6 +212,16 @@ struct ProfScope {
 };
 void prof_collect(bfq_ctx *c);   // resolves pending event pairs (after a stream sync)
 
+// Keeps [ptr, ptr + bytes) in the persisting part of L2 for the kernels launched on the context's stream while the
+// object lives (as much of it as the set-aside takes: the hit ratio is scaled), everything else streams through.
+struct L2Pin {
+    cudaStream_t st = nullptr; bool on = false;
+    L2Pin(bfq_ctx *c, const void *ptr, size_t bytes);
+    ~L2Pin();
+    L2Pin(const L2Pin &) = delete;
+    L2Pin &operator=(const L2Pin &) = delete;
+};
+
 template <typename T> inline T *arena_alloc(bfq_ctx *c, size_t count)
 {
     return (T *)c->arena.alloc(count * sizeof(T));

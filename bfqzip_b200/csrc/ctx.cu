@@ -5,6 +5,33 @@
 
 namespace bfq {
 
+L2Pin::L2Pin(bfq_ctx *c, const void *ptr, size_t bytes)
+{
+    if (!bytes || c->l2_persist_max == 0 || c->l2_window_max == 0) return;
+    const size_t want = std::min(c->l2_persist_max, bytes + (bytes >> 3));
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) != cudaSuccess) { cudaGetLastError(); return; }
+    cudaStreamAttrValue av;
+    memset(&av, 0, sizeof av);
+    av.accessPolicyWindow.base_ptr = const_cast<void *>(ptr);
+    av.accessPolicyWindow.num_bytes = std::min(bytes, c->l2_window_max);
+    av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)av.accessPolicyWindow.num_bytes);
+    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    st = c->stream;
+    on = cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+    if (!on) cudaGetLastError();
+}
+
+L2Pin::~L2Pin()
+{
+    if (!on) return;
+    cudaStreamAttrValue av;
+    memset(&av, 0, sizeof av);
+    cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
+    cudaCtxResetPersistingL2Cache();
+    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0);   // give the set-aside back
+}
+
 __global__ void fetch_small_kernel(uint32_t *__restrict__ host_dst, const uint32_t *__restrict__ src, uint32_t words)
 {
     for (uint32_t i = threadIdx.x; i < words; i += blockDim.x) host_dst[i] = src[i];

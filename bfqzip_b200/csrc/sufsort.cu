@@ -919,31 +919,7 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
     c->trace("suffix keys sorted", st);
     // The packed text is what every group gathers from at random: pin it in L2 (persisting access
     // window, set aside only for the group kernels) while the sorted list streams through; T3 of config 2 is 38 MB of the 126 MB L2.
-    const size_t t3_bytes = (ngroups * 3 + 2) * 8;
-    bool pinned = false;
-    if (c->l2_persist_max > 0 && c->l2_window_max > 0 &&
-        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min(c->l2_persist_max, t3_bytes + (t3_bytes >> 3))) == cudaSuccess) {
-        cudaStreamAttrValue av;
-        memset(&av, 0, sizeof av);
-        av.accessPolicyWindow.base_ptr = T3;
-        av.accessPolicyWindow.num_bytes = std::min(t3_bytes, c->l2_window_max);
-        av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)std::min(c->l2_persist_max, t3_bytes + (t3_bytes >> 3)) / (double)av.accessPolicyWindow.num_bytes);
-        av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-        av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-        pinned = cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
-        if (!pinned) cudaGetLastError();
-    }
-    struct Unpin {
-        cudaStream_t st; bool on;
-        ~Unpin() {
-            if (!on) return;
-            cudaStreamAttrValue av;
-            memset(&av, 0, sizeof av);
-            cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &av);
-            cudaCtxResetPersistingL2Cache();
-            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0);   // give the set-aside back to parts B and C
-        }
-    } unpin{st, pinned};
+    L2Pin pin_text(c, T3, (ngroups * 3 + 2) * 8);
 
     auto words_for = [&](int depth) { return (int)std::max<int64_t>(0, ((int64_t)max_len - depth + 20) / 21); };
     GroupTileArgsT<P> G;

@@ -103,6 +103,46 @@ def test_part_a_huge_groups():
     assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
 
 
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_part_a_majority_reference(seed):
+    """In-group ordering compares every member with a string voted from the three longest members: groups whose longest
+    members disagree pairwise at the same symbol (the vote yields a symbol none of them has), whose longest member carries
+    errors, with two or three members only, with many members of equal length, and with N inside the tails."""
+    rng = np.random.default_rng(seed)
+    L = 90
+    loci = [bytes(rng.choice(list(b"ACGT"), size=2 * L).astype(np.uint8)) for _ in range(40)]
+    reads = []
+    for li, g in enumerate(loci):
+        cover = [2, 3, 5, 31, 33, 47, 64, 70][li % 8]             # group sizes around the 32 / 64 row paths
+        for r in range(cover):
+            s0 = int(rng.integers(0, L // 2))
+            n = int(rng.integers(30, L)) if li % 3 else L             # li % 3 == 0: every member has the same length
+            rd = bytearray(g[s0:s0 + n])
+            mode = (li + r) % 5
+            if mode == 0 and len(rd) > 40:                            # all reads of the locus disagree at one fixed symbol
+                rd[40 - s0 if 40 - s0 >= 0 else 0] = b"ACGTN"[r % 5]
+            elif mode == 1:                                           # a random error
+                i = int(rng.integers(0, len(rd))); rd[i] = b"ACGT"[int(rng.integers(0, 4))]
+            elif mode == 2 and len(rd) > 25:
+                rd[int(rng.integers(20, len(rd)))] = ord("N")
+            reads.append(bytes(rd))
+    reads += [bytes(loci[0][:70])] * 5                                # identical reads: ties go to read order
+    order = rng.permutation(len(reads))
+    reads = [reads[i] for i in order]
+    bases = np.frombuffer(b"".join(reads), dtype=np.uint8)
+    off = np.zeros(len(reads) + 1, np.uint64); off[1:] = np.cumsum([len(r) for r in reads])
+    quals = rng.integers(35, 74, size=bases.size, dtype=np.uint8)
+    c = ctx()
+    for k in (0, 6):                                                  # default key and a short one (larger groups)
+        c.set_option("initial_k", k)
+        try:
+            bwt, qs, lcp = c.build_ebwt(bases, quals, off, 35)
+        finally:
+            c.set_option("initial_k", 0)
+        rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+        assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+
+
 def test_part_a_refuses_reads_longer_than_255():
     """LCP entries are one byte and dataTypelenSeq is uchar (parameters.h:68): longer reads are an error, not a wrap."""
     bases = np.frombuffer(b"ACGT" * 80, dtype=np.uint8)
