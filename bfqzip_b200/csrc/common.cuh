@@ -183,6 +183,7 @@ struct bfq_ctx {
     int opt_initial_k = 0;
     int64_t opt_long_cluster = 1024;
     int64_t opt_group_cap = 1 << 20;
+    int64_t opt_batch_min_groups = 64;    // group_tile_kernel: tiles with more groups than this order them in batches
     int opt_rebuild = 0;                  // fused pipeline, part C: 0 auto, 1 streaming un-permute (flat), 2 inverse-LF walk
     int64_t opt_flat_min_rows = 1 << 28;  // auto: flat mode from this many rows on
     int opt_profile = 0;

@@ -240,6 +240,7 @@ int bfq_ctx_set_option(bfq_ctx *c, const char *key, int64_t value)
     if (k == "initial_k") { if (value < 0 || value > 21) { set_error("initial_k must be 0..21"); return BFQ_EINVAL; } c->opt_initial_k = (int)value; }
     else if (k == "long_cluster") { if (value < 4) { set_error("long_cluster must be >= 4"); return BFQ_EINVAL; } c->opt_long_cluster = value; }
     else if (k == "group_cap") { if (value < 1) { set_error("group_cap must be >= 1"); return BFQ_EINVAL; } c->opt_group_cap = value; }
+    else if (k == "batch_min_groups") { if (value < 0) { set_error("batch_min_groups must be >= 0"); return BFQ_EINVAL; } c->opt_batch_min_groups = value; }
     else if (k == "rebuild") { if (value < 0 || value > 2) { set_error("rebuild must be 0 (auto), 1 (un-permute) or 2 (LF walk)"); return BFQ_EINVAL; } c->opt_rebuild = (int)value; }
     else if (k == "flat_min_rows") { if (value < 0) { set_error("flat_min_rows must be >= 0"); return BFQ_EINVAL; } c->opt_flat_min_rows = value; }
     else if (k == "profile") c->opt_profile = value ? 1 : 0;

@@ -151,6 +151,7 @@ constexpr int GT_E = 256;
 constexpr int GT_S = GT_T + GT_E;
 constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
 constexpr int GT_GMAX = GT_S / 2;
+constexpr int GT_BATCH = 48;                          // rows of a tile whose groups form one batch (see phase 1b)
 constexpr int GT_RW = 13;                             // words of 21 symbols that hold the longest suffix tail (255 symbols)
 
 template <typename P>
@@ -178,6 +179,7 @@ struct GroupTileArgsT {
     uint64_t kmask;             // key bits that take part in group equality (level 0: the 3*ksym symbol bits)
     int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
+    uint32_t batch_min_groups;  // tiles with more groups than this are ordered batch-wise
 };
 using GroupTileArgs = GroupTileArgsT<uint32_t>;
 
@@ -290,11 +292,14 @@ __device__ __forceinline__ uint32_t class_l(uint32_t cls)
     return ((cls >> 11) & 3u) == 2u ? 255u - lk : lk;
 }
 
-// groups of at most 32 * R rows: one row per (slot, lane), keys in registers, shuffles only
-template <int R, typename P>
+// groups of at most 32 * R rows: one row per (slot, lane), keys in registers, shuffles only.
+// MULTI: the rows [gs, gs + len) are a BATCH of whole small groups and single rows (low coverage leaves a few rows per
+// group; a warp per group would idle most lanes): every group starts as its own run -- the same state a single group
+// is in after its first iteration -- and all of them are ordered by the same sorting network.
+template <int R, bool MULTI, typename P>
 __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int lane, int depth, const uint64_t *__restrict__ T3,
                                                  const P *s_pos, const uint8_t *s_len, uint32_t *s_best, uint16_t *s_sorted,
-                                                 uint8_t *s_lcpout, uint64_t *s_refw)
+                                                 uint8_t *s_lcpout, uint64_t *s_refw, const uint16_t *s_gs)
 {
     constexpr uint32_t IB = 6, IM = 63u;                  // position index bits
     uint32_t key[R], runa[R], rdepth[R];
@@ -305,7 +310,24 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
         runa[s] = 0;
         rdepth[s] = t < len ? 0u : 0xFFu;
     }
-    {   // V: the three longest members (valid bit | length | row), then lane j builds word j
+    bool first = !MULTI;
+    if constexpr (MULTI) {
+        bool work = false;
+#pragma unroll
+        for (int s = 0; s < R; s++) {
+            const uint32_t t = s * 32 + lane;
+            if (t < len) {
+                const uint32_t row = gs + t, g0 = s_gs[row];      // (0xFFFF: a group handed to the next level, its rows stay put)
+                const bool head = g0 == row;
+                const bool single = g0 == 0xFFFFu || (head && (t + 1 >= len || s_gs[row + 1] != g0));
+                runa[s] = single ? t : g0 - gs;
+                if (single) rdepth[s] = 0xFFu;
+                else { work = true; if (head) s_best[row] = 0; }
+            }
+        }
+        if (!__any_sync(0xffffffffu, work)) return;       // single rows only: s_sorted is the identity already
+        __syncwarp();
+    } else {   // V: the three longest members (valid bit | length | row), then lane j builds word j
         uint32_t v[R], a = 0, b = 0, cc = 0;
 #pragma unroll
         for (int s = 0; s < R; s++) {
@@ -337,7 +359,6 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
         }
         __syncwarp();
     }
-    bool first = true;
     while (true) {
         if (!first) {
 #pragma unroll
@@ -355,8 +376,9 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
                 const uint32_t idx = key[s] & IM;
                 if (rdepth[s] == 0xFFu) key[s] = (t << (13 + IB)) | idx;
                 else {
-                    const RefCmp o = first ? v_compare(T3, s_refw, (uint64_t)s_pos[gs + idx] + depth, s_len[gs + idx])
-                                           : ref_compare(T3, s_pos, s_len, depth, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
+                    RefCmp o;
+                    if (!MULTI && first) o = v_compare(T3, s_refw, (uint64_t)s_pos[gs + idx] + depth, s_len[gs + idx]);
+                    else o = ref_compare(T3, s_pos, s_len, depth, gs + idx, s_best[gs + runa[s]] & 0xFFFFu, rdepth[s]);
                     key[s] = (runa[s] << (13 + IB)) | (class_of(o) << IB) | idx;
                 }
             }
@@ -533,7 +555,7 @@ __device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int 
 }
 
 template <typename K, typename P>
-__global__ void __launch_bounds__(GT_THREADS)
+__global__ void __launch_bounds__(GT_THREADS, 5)
 group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
@@ -663,16 +685,50 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     }
     __syncthreads();
 
-    // ---- phase 2: one warp orders one group
+    // ---- phase 1b: a tile of many small groups (low coverage) is cut into BATCHES instead -- batch i = the groups that
+    // start in rows [i * GT_BATCH, (i + 1) * GT_BATCH) -- and a warp orders a whole batch at once.  Only the last group of a
+    // batch can be longer than GT_BATCH rows; it becomes a work item of its own when the batch would exceed 64 rows.
+    if (s_ngroups > A.batch_min_groups) {                // (block-uniform)
+        __syncthreads();
+        if (tid == 0) s_ngroups = 0;
+        __syncthreads();
+        constexpr int NBATCH = (GT_T + GT_BATCH - 1) / GT_BATCH;
+        if (tid < NBATCH) {
+            const int lo = tid * GT_BATCH, hi = min(lo + GT_BATCH, GT_T);
+            const int last = (int)min((uint64_t)GT_S, (uint64_t)m - t0);          // rows of the window inside the list
+            const int a = next_head(lo - 1);
+            int b = min(next_head(hi - 1), last);
+            if (a < hi && a < b) {
+                if (s_gs[b - 1] == 0xFFFFu) b = prev_head(b - 1);               // the last group does not fit the window: deferred
+                if (b - a > 64) {
+                    const int ls = prev_head(b - 1);
+                    const uint32_t g = atomicAdd(&s_ngroups, 1u);
+                    s_gstart[g] = (uint16_t)ls; s_glen[g] = (uint16_t)(b - ls);
+                    b = ls;
+                }
+                if (b - a > 1) {
+                    const uint32_t g = atomicAdd(&s_ngroups, 1u);
+                    s_gstart[g] = (uint16_t)a; s_glen[g] = (uint16_t)((b - a) | 0x8000);
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---- phase 2: one warp orders one group (or one batch of small groups)
     const uint32_t ngroups = s_ngroups;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&s_next, 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
-        const uint32_t gs = s_gstart[g], len = s_glen[g];
-        if (len <= 32) order_group_regs<1, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw);
-        else if (len <= 64) order_group_regs<2, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw);
+        const uint32_t gs = s_gstart[g], len = s_glen[g] & 0x7FFFu;
+        if (s_glen[g] & 0x8000u) {
+            if (len <= 32) order_group_regs<1, true, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, s_gs);
+            else order_group_regs<2, true, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, s_gs);
+        }
+        else if (len <= 32) order_group_regs<1, false, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, s_gs);
+        else if (len <= 64) order_group_regs<2, false, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, s_gs);
         else order_group_smem<P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_key, s_runa, s_rdepth);
         __syncwarp();
     }
@@ -927,6 +983,7 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
     G.T3 = T3; G.QL = QL; G.SA = d_sa_out; G.bwt = d_bwt; G.qs = d_qs; G.lcp = d_lcp;
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
     G.group_cap = (uint32_t)c->opt_group_cap;
+    G.batch_min_groups = (uint32_t)c->opt_batch_min_groups;
     G.prev_key = prev_key; G.has_prev = has_prev;
 
     int parity = 0, depth = 0, ksym = k, level = 0;

@@ -15,10 +15,10 @@ sys.path.insert(0, ROOT)
 import numpy as np  # noqa: E402
 
 
-def torch_reads(torch, dev, nreads, L, seed):
+def torch_reads(torch, dev, nreads, L, seed, glen=0):
     """synth.make_reads' model (40x coverage, SNP haplotype, 1 % errors, an N every 1000th read) generated on the device."""
     gen = torch.Generator(device=dev); gen.manual_seed(seed)
-    glen = max(L + 1, nreads * L // 40)
+    glen = glen or max(L + 1, nreads * L // 40)
     hap = torch.randint(0, 4, (2, glen), device=dev, dtype=torch.uint8, generator=gen)
     hap[1] = hap[0]
     snp = torch.arange(500, glen, 1000, device=dev)
@@ -50,6 +50,7 @@ def main():
     ap.add_argument("--B", type=int, default=0)
     ap.add_argument("--seed", type=int, default=1001)
     ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--glen", type=int, default=0, help="--torchgen: genome length (default: 40x coverage)")
     ap.add_argument("--torchgen", action="store_true", help="generate the reads on the GPU (large collections) and run size-independent checks")
     ap.add_argument("--opt", action="append", default=[], help="ctx option key=value (repeatable)")
     ap.add_argument("--stages", action="store_true", help="print the per-stage CUDA-event times")
@@ -59,7 +60,7 @@ def main():
     from bfqzip_b200 import lib, synth
     dev = torch.device("cuda", 0)
     if a.torchgen:
-        d_b, d_q, off = torch_reads(torch, dev, a.nreads, a.len, a.seed)
+        d_b, d_q, off = torch_reads(torch, dev, a.nreads, a.len, a.seed, a.glen)
         bases = quals = None
     else:
         bases, quals, off = synth.make_reads(a.nreads, a.len, a.seed)

@@ -143,6 +143,35 @@ def test_part_a_majority_reference(seed):
         assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
 
 
+@pytest.mark.parametrize("cov,min_groups", [(3, 0), (6, 0), (40, 0), (5, 64)])
+def test_part_a_batched_small_groups(cov, min_groups):
+    """Low coverage leaves a few rows per group: tiles with many groups order them in batches of whole groups and single
+    rows (one warp per batch instead of one per group).  batch_min_groups = 0 forces that path on every tile."""
+    nreads, L = 6000, 100
+    bases, quals, off = synth.make_reads(nreads, L, 77 + cov, coverage=cov)
+    c = ctx()
+    c.set_option("batch_min_groups", min_groups)
+    try:
+        bwt, qs, lcp = c.build_ebwt(bases, quals, off, 35)
+    finally:
+        c.set_option("batch_min_groups", 64)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    assert np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+
+
+@pytest.mark.parametrize("cap", [2, 3, 5])
+def test_part_a_batched_with_deferred_groups(cap):
+    """Batches that contain groups handed to the next MSD level (group_cap): their rows stay put inside the batch."""
+    g = np.load(os.path.join(H.GOLDEN, "syn_var_dup.npz"))
+    c = ctx()
+    c.set_option("batch_min_groups", 0); c.set_option("group_cap", cap)
+    try:
+        bwt, qs, lcp = c.build_ebwt(g["bases"], g["quals"], g["off"], 35)
+    finally:
+        c.set_option("batch_min_groups", 64); c.set_option("group_cap", 1 << 20)
+    assert np.array_equal(bwt, g["bwt"]) and np.array_equal(qs, g["qs"]) and np.array_equal(lcp, g["lcp"])
+
+
 def test_part_a_refuses_reads_longer_than_255():
     """LCP entries are one byte and dataTypelenSeq is uchar (parameters.h:68): longer reads are an error, not a wrap."""
     bases = np.frombuffer(b"ACGT" * 80, dtype=np.uint8)
