@@ -185,18 +185,6 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     const uint32_t tile_base = tile * (uint32_t)TILE;
     const uint32_t valid = min((uint32_t)TILE, n - tile_base);
 
-    // ---- the tile that starts when this one ends (about one wave of resident CTAs later) is pulled into L2 now, so the
-    // loads at the top of a CTA see L2 latency instead of DRAM latency
-    {
-        const uint64_t ahead = ((uint64_t)tile + 148u * RS_BLOCKS_PER_SM(ITEMS)) * TILE;
-        if (ahead < n) {
-            const char *kp = reinterpret_cast<const char *>(keys_in + ahead);
-            const char *vp = reinterpret_cast<const char *>(vals_in + ahead);
-            for (uint32_t o = tid * 128u; o < TILE * sizeof(K); o += RS_THREADS * 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(kp + o));
-            for (uint32_t o = tid * 128u; o < TILE * sizeof(V); o += RS_THREADS * 128u) asm volatile("prefetch.global.L2 [%0];" ::"l"(vp + o));
-        }
-    }
-
     // ---- load keys (warp-striped: item i of lane l sits at warp_base + i*32 + l)
     K key[ITEMS];
     const uint32_t wbase = w * (ITEMS * 32) + lane;

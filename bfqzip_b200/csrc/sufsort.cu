@@ -151,7 +151,10 @@ constexpr int GT_E = 256;
 constexpr int GT_S = GT_T + GT_E;
 constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
 constexpr int GT_GMAX = GT_S / 2;
-constexpr int GT_BATCH = 48;                          // rows of a tile whose groups form one batch (see phase 1b)
+#ifndef GT_BATCH_ROWS
+#define GT_BATCH_ROWS 48
+#endif
+constexpr int GT_BATCH = GT_BATCH_ROWS;                          // rows of a tile whose groups form one batch (see phase 1b)
 constexpr int GT_RW = 13;                             // words of 21 symbols that hold the longest suffix tail (255 symbols)
 
 template <typename P>
