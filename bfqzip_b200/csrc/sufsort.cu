@@ -226,7 +226,7 @@ __device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, c
 {
     // The strings are read straight from the packed text (L1 / pinned L2): a member is compared once per
     // iteration, so staging it in shared memory would cost more than it saves (and occupancy with it).
-    const uint32_t lm = s_len[mem], lr = s_len[ref];      // the reference is its run's longest member: lm <= lr
+    const uint32_t lm = s_len[mem];                       // the reference is its run's longest member: lm <= its length
     const uint64_t pm = (uint64_t)s_pos[mem] + depth, pr = (uint64_t)s_pos[ref] + depth;
     RefCmp o;
     o.l = lm; o.c = 0u;
@@ -247,8 +247,10 @@ __device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, c
             }
         }
     }
-    // the member is a prefix of the reference (or the reference itself): c = its terminator
-    o.r = lm < lr ? sym_code(T3, pr + lm) : 0u;
+    // The member is a prefix of the reference (or the reference itself): c = its terminator.  What the reference holds
+    // there does not matter -- a terminator sorts below every symbol and equal strings keep their position order --
+    // so the row is classed "below the reference at l = its length" without reading it.
+    o.r = 1u;
     return o;
 }
 
@@ -277,8 +279,7 @@ __device__ __forceinline__ RefCmp v_compare(const uint64_t *__restrict__ T3, con
             break;
         }
     }
-    const uint32_t j = lm / 21u, f = lm - 21u * j;        // V's symbol after the member's last one (0 = a's terminator)
-    o.r = (uint32_t)((s_v[j] << (3u * f)) >> 61);
+    o.r = 1u;                                             // a prefix of V: below it at l = its length (see ref_compare)
     return o;
 }
 
