@@ -154,12 +154,15 @@ template <int B> __device__ __forceinline__ void match_bit(uint32_t d, uint32_t 
                  : "+r"(m) : "r"(d), "n"(1u << B));
 }
 
-template <typename K, typename V, typename S, int ITEMS>
+// EMIT = true: the first pass of the flat-mode rebuild makes its input on the fly from the smoothed rows -- element i is
+// (text position SA[i] - 1, base | quality << 8), see PermSource in common.cuh -- so the pair list is never written
+// unsorted and read back (the loads are as many bytes as the pairs would be).
+template <typename K, typename V, typename S, int ITEMS, bool EMIT = false>
 __global__ void __launch_bounds__(RS_THREADS, RS_BLOCKS_PER_SM(ITEMS))
 rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
                    const V *__restrict__ vals_in, V *__restrict__ vals_out,
                    uint32_t n, int shift, int bits, const uint32_t *__restrict__ digit_base,
-                   S *__restrict__ status, uint32_t *__restrict__ tile_counter)
+                   S *__restrict__ status, uint32_t *__restrict__ tile_counter, PermSource src = PermSource{})
 {
     constexpr int TILE = RS_THREADS * ITEMS;
     static_assert(sizeof(V) <= sizeof(K), "the payload is staged in the key buffer");
@@ -191,7 +194,11 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t loc = wbase + i * 32;
-        key[i] = (loc < valid) ? keys_in[tile_base + loc] : (K)~(K)0;
+        if constexpr (EMIT) {
+            key[i] = (K)~(K)0;
+            if (loc < valid) { const uint32_t p = src.SA[tile_base + loc]; key[i] = (K)(p ? p - 1 : src.n_total - 1); }
+        } else
+            key[i] = (loc < valid) ? keys_in[tile_base + loc] : (K)~(K)0;
     }
     // ---- stable in-warp ranking
     uint16_t rank[ITEMS];
@@ -258,7 +265,16 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 #pragma unroll
     for (int i = 0; i < ITEMS; i++) {
         uint32_t loc = wbase + i * 32;
-        val[i] = (loc < valid) ? vals_in[tile_base + loc] : (V)0;
+        if constexpr (EMIT) {
+            val[i] = (V)0;
+            if (loc < valid) {
+                const uint32_t r = tile_base + loc;
+                const uint8_t q = src.qflat[r];
+                const uint8_t base = (q & 0x80) ? src.obase[r] : src.bwt[r];
+                val[i] = (V)(base | ((uint32_t)(q & 0x7F) << 8));
+            }
+        } else
+            val[i] = (loc < valid) ? vals_in[tile_base + loc] : (V)0;
     }
 
     // ---- chained scan: exclusive prefix of this digit over all earlier tiles
@@ -307,7 +323,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 // the passes, given the (unscanned) digit histograms of all of them
 template <typename K, typename V, int ITEMS>
 static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, uint64_t n,
-                        const RsPasses &P, uint32_t *hist)
+                        const RsPasses &P, uint32_t *hist, const PermSource *src = nullptr)
 {
     constexpr int TILE = RS_THREADS * ITEMS;
     const uint32_t tiles = div_up(n, TILE);
@@ -330,6 +346,22 @@ static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, 
         {
             ProfScope ps(c, PC_RADIX_PASS, 2 * n * (sizeof(K) + sizeof(V)));
             const size_t dyn = (size_t)TILE * sizeof(K);
+            if constexpr (sizeof(K) == 4 && sizeof(V) == 2) {
+                if (src && p == 0) {
+                    if (wide)
+                        rs_onesweep_kernel<K, V, uint64_t, ITEMS, true><<<tiles, RS_THREADS, dyn, c->stream>>>(
+                            kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
+                            (uint64_t *)status, tile_counter, *src);
+                    else
+                        rs_onesweep_kernel<K, V, uint32_t, ITEMS, true><<<tiles, RS_THREADS, dyn, c->stream>>>(
+                            kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
+                            (uint32_t *)status, tile_counter, *src);
+                    BFQ_CUDA(cudaGetLastError());
+                    std::swap(kin, kout);
+                    std::swap(vin, vout);
+                    continue;
+                }
+            }
             if (wide)
                 rs_onesweep_kernel<K, V, uint64_t, ITEMS><<<tiles, RS_THREADS, dyn, c->stream>>>(
                     kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
@@ -619,8 +651,15 @@ rs_place_kernel(const uint32_t *__restrict__ keys, const uint16_t *__restrict__ 
     }
 }
 
-int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n)
+bool radix_permutation_generates(uint64_t n)
 {
+    return n > ((uint64_t)1 << PL_BITS) && n < ((uint64_t)1 << 32);      // at least one pass above the placement bits
+}
+
+int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n,
+                           const PermSource *src)
+{
+    if (src && !radix_permutation_generates(n)) BFQ_FAIL(BFQ_ECUDA, "internal error: no radix pass to generate the pairs in");
     if (n == 0) return 0;
     if (n >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "radix sort: n=%llu needs 64-bit indices", (unsigned long long)n);
     int bits = 1;
@@ -638,7 +677,7 @@ int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint1
             for (uint32_t d = 0; d < (1u << P.bits[p]); d++) h[p * RS_RADIX + d] = count_digit(n, P.shift[p], P.bits[p], d);
         // pageable source: the copy is staged by the runtime before the call returns
         BFQ_CUDA(cudaMemcpyAsync(hist, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-        flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist);
+        flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist, src);
     }
     if (low) {
         const size_t smem = sizeof(uint16_t) << PL_BITS;

@@ -201,12 +201,15 @@ void unpermute_dev(bfq_ctx *c, const SmoothResult &S, const uint8_t *d_bwt, cons
     Arena::Mark mk = c->arena.mark();
     uint32_t *ka = arena_alloc<uint32_t>(c, n + 16), *kb = arena_alloc<uint32_t>(c, n + 16);
     uint16_t *va = arena_alloc<uint16_t>(c, n + 16), *vb = arena_alloc<uint16_t>(c, n + 16);
-    {
+    // the first sort pass reads the smoothed rows itself whenever the sort has one; tiny collections emit the pairs first
+    const bool fused = radix_permutation_generates(n);
+    const PermSource src{d_sa, d_bwt, S.lines, S.obase, (uint32_t)n};
+    if (!fused) {
         ProfScope ps(c, PC_WALK, n * (4 + 3 + 6));
         emit_pairs_kernel<<<div_up(n, 256), 256, 0, st>>>(d_sa, d_bwt, S.lines, S.obase, (uint32_t)n, ka, va, (uint32_t)n);
         BFQ_CUDA(cudaGetLastError());
     }
-    const int flip = radix_sort_permutation(c, ka, kb, va, vb, n);
+    const int flip = radix_sort_permutation(c, ka, kb, va, vb, n, fused ? &src : nullptr);
     {
         ProfScope ps(c, PC_ASSEMBLE, n * 2 + (n - nreads) * 2);
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 16, div_up(nreads * 32, 256));

@@ -315,6 +315,10 @@ struct SmoothLists {
 // A tile writes the stored quality of every row it owns: all rows except its leading run of
 // flagged rows (those belong to a cluster that started in an earlier tile, whose owner writes them).
 constexpr int CL_THREADS = 256;
+#ifndef CLT_THREADS_N
+#define CLT_THREADS_N 128
+#endif
+constexpr int CLT_THREADS = CLT_THREADS_N;   // tile kernel: a tile holds ~120 clusters, one thread each
 constexpr int CL_TILE = 4096;
 constexpr int CL_EXT = 512;                 // rows staged past the tile: a cluster that starts in the tile and ends inside
 constexpr int CL_S = CL_TILE + CL_EXT;      // the staged window is finished here, longer ones go to cluster_long_kernel
@@ -335,7 +339,7 @@ __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stat
 }
 
 template <bool FLAT>
-__global__ void __launch_bounds__(CL_THREADS, 6)
+__global__ void __launch_bounds__(CLT_THREADS, 1536 / CLT_THREADS)
 cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
                     uint8_t *__restrict__ obase, SmoothLists L)
@@ -351,14 +355,14 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     const int tid = threadIdx.x;
     const int64_t t0 = (int64_t)blockIdx.x * CL_TILE;
     const int64_t nn = (int64_t)n;
-    s_lut[tid] = g_sc.byte2code[tid];
+    for (int i = tid; i < 256; i += CLT_THREADS) s_lut[i] = g_sc.byte2code[i];
     if (tid == 0) { s_nstarts = 0; s_lead = CL_TILE; }
     if (tid < ST_COUNT) s_stats[tid] = 0;
     __syncthreads();
     // ---- staging, 16 rows per thread and step: codes, qualities and the rule 5-6 flags (3-point stencil on the LCP,
     // computed in registers: the LCP itself is not kept).  Chunk CL_S / 16 only supplies the flag of row t0 + CL_S.
     const bool vec = ((reinterpret_cast<uintptr_t>(bwt) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(lcp)) & 15) == 0;
-    for (int k = tid; k <= CL_S / 16; k += CL_THREADS) {
+    for (int k = tid; k <= CL_S / 16; k += CLT_THREADS) {
         const int r0 = 16 * k;
         const int64_t i0 = t0 + r0;
         uint32_t wl[4] = {0, 0, 0, 0}, cw[4] = {0, 0, 0, 0}, qw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0};     // 16 packed bytes each
@@ -401,7 +405,7 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     __syncthreads();
 
     // ---- cluster starts and the leading run
-    for (int k = tid; k < CL_TILE / 16; k += CL_THREADS) {
+    for (int k = tid; k < CL_TILE / 16; k += CLT_THREADS) {
         const int r0 = 16 * k;
         if (t0 + r0 >= nn) break;
         const uint4 v = *reinterpret_cast<const uint4 *>(s_f + r0);
@@ -425,7 +429,7 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
 #pragma unroll
     for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
 
-    for (uint32_t idx = tid; idx < nstarts; idx += CL_THREADS) {
+    for (uint32_t idx = tid; idx < nstarts; idx += CLT_THREADS) {
         const int a = s_starts[idx];
         int e = a + 1;
         while (e <= CL_S && s_f[e]) e++;
@@ -478,7 +482,7 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     __syncthreads();
     // ---- stored qualities of the rows this tile owns
     const uint32_t lead = s_lead;
-    for (int k = tid; k < CL_TILE / 16; k += CL_THREADS) {
+    for (int k = tid; k < CL_TILE / 16; k += CLT_THREADS) {
         const int r0 = 16 * k;
         const int64_t i0 = t0 + r0;
         if (i0 >= nn || (uint32_t)(r0 + 15) < lead) continue;
@@ -797,8 +801,8 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     BFQ_CUDA(cudaMemsetAsync(d_stats, 0, (ST_COUNT + 2) * 8, st));
     {
         ProfScope ps(c, PC_CLUSTER, 4 * n);
-        if (flat) cluster_tile_kernel<true><<<div_up(n, CL_TILE), CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
-        else cluster_tile_kernel<false><<<div_up(n, CL_TILE), CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        if (flat) cluster_tile_kernel<true><<<div_up(n, CL_TILE), CLT_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+        else cluster_tile_kernel<false><<<div_up(n, CL_TILE), CLT_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
         launch_check(c);
     }
     {
