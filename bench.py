@@ -145,7 +145,7 @@ def reference_arm(args):
             "cpu_baseline": {"value": val, "unit": "Gbases/s", "cores": cores if kind == "reference" else 1, "kind": kind, "sample": sample},
             "e2e": {"value": val, "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------- GPU arm
@@ -292,7 +292,7 @@ def gpu_arm(args):
             "clocks": sampler.summary(),
             "stats": st,
         }
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -305,10 +305,26 @@ def main():
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE line, the JSON: while the arms run, file descriptor 1 points at stderr (libraries such as
+    # NCCL write banners to it from native code); print() is given the real stdout back through _emit
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    global _OUT
+    _OUT = os.fdopen(real, "w")
     if args.impl == "reference":
         reference_arm(args)
     else:
         gpu_arm(args)
+
+
+_OUT = None
+
+
+def _emit(line):
+    out = _OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 if __name__ == "__main__":
