@@ -80,6 +80,8 @@ void bfq_ctx_destroy(bfq_ctx *ctx);
 /* Tunables (tests use them to force rarely-taken paths).  Unknown key -> BFQ_EINVAL.
  *   "initial_k"   symbols in the initial radix key (1..21, 0 = auto)
  *   "group_cap"   suffix groups with more members go to the next MSD level even when they fit a tile
+ *   "batch_min_groups" a tile of the sorted suffix list with more groups than this (default 64: low coverage, a few rows per
+ *                 group) is ordered in batches of whole groups, one warp per batch, instead of one warp per group; 0 = always
  *   "rebuild"     part C of the fused pipeline: 0 auto, 1 streaming un-permute through the suffix array, 2 inverse-LF walk
  *   "flat_min_rows" auto mode switches to the un-permute from this many BWT rows on
  *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
