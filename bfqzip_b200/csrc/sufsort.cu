@@ -146,8 +146,14 @@ pack3_kernel(const uint8_t *__restrict__ T8, uint64_t n, uint64_t ngroups, uint6
 // start is appended to a list and the host runs one more level on those groups with the next
 // symbols as key (MSD recursion; at most ceil(max_len / 14) levels, only repeats get there).
 constexpr int GT_THREADS = 256;
-constexpr int GT_T = 1024;
-constexpr int GT_E = 256;
+#ifndef GT_T_ROWS
+#define GT_T_ROWS 1024
+#endif
+#ifndef GT_E_ROWS
+#define GT_E_ROWS 256
+#endif
+constexpr int GT_T = GT_T_ROWS;
+constexpr int GT_E = GT_E_ROWS;
 constexpr int GT_S = GT_T + GT_E;
 constexpr int GT_HW = (GT_S + 1 + 31) / 32 + 1;       // head bitmap words (bit GT_S is the sentinel)
 constexpr int GT_GMAX = GT_S / 2;
@@ -447,6 +453,7 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
             startbits[s] = __ballot_sync(0xffffffffu, t < len && st[s]);
             any |= un[s];
         }
+        if (!__any_sync(0xffffffffu, any)) break;         // everything resolved: no run bookkeeping needed
 #pragma unroll
         for (int s = 0; s < R; s++) {
             const uint32_t t = s * 32 + lane;
@@ -460,7 +467,6 @@ __device__ __forceinline__ void order_group_regs(uint32_t gs, uint32_t len, int 
             }
         }
         __syncwarp();
-        if (!__any_sync(0xffffffffu, any)) break;
     }
 #pragma unroll
     for (int s = 0; s < R; s++) {
@@ -592,18 +598,20 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     // the window sits at s_key[r + 1]; [0] is the key before the window, [GT_S + 1] the one after it), then the head
     // bitmap: bit r <=> list slot t0 + r starts a group
     {
-        constexpr int NB = GT_S / GT_THREADS;
+        constexpr int NB = (GT_S + GT_THREADS - 1) / GT_THREADS;
         K kk[NB]; P pp[NB];
 #pragma unroll
         for (int i = 0; i < NB; i++) {
             const uint64_t j = (uint64_t)t0 + i * GT_THREADS + tid;
-            kk[i] = j < m ? __ldcs(&keys[j]) : (K)0;
-            pp[i] = j < m ? __ldcs(&A.pos[j]) : (P)0;
+            const bool in = i * GT_THREADS + tid < GT_S && j < m;
+            kk[i] = in ? __ldcs(&keys[j]) : (K)0;
+            pp[i] = in ? __ldcs(&A.pos[j]) : (P)0;
         }
         if (tid == 0) s_key[0] = t0 > 0 ? keys[t0 - 1] : (K)0;
         if (tid == 32) s_key[GT_S + 1] = (uint64_t)t0 + GT_S < m ? keys[(uint64_t)t0 + GT_S] : (K)0;
 #pragma unroll
-        for (int i = 0; i < NB; i++) { s_key[i * GT_THREADS + tid + 1] = kk[i]; s_pos[i * GT_THREADS + tid] = pp[i]; }
+        for (int i = 0; i < NB; i++)
+            if (i * GT_THREADS + tid < GT_S) { s_key[i * GT_THREADS + tid + 1] = kk[i]; s_pos[i * GT_THREADS + tid] = pp[i]; }
     }
     __syncthreads();
     for (int base = 0; base < GT_HW * 32; base += GT_THREADS) {
