@@ -125,31 +125,41 @@ rank_count_kernel(const uint8_t *__restrict__ bwt, uint64_t n, uint32_t *__restr
     if (threadIdx.x < 5) blk_counts[(size_t)blockIdx.x * 8 + threadIdx.x] = s_cnt[threadIdx.x];
 }
 
-// single block: exclusive scan over blocks for each code, plus the pile start C[code]
+// single block: exclusive scan over blocks for each code, plus the pile start C[code] (the five codes side by side)
 __global__ void __launch_bounds__(1024)
 rank_scan_kernel(uint32_t *__restrict__ blk_counts, uint32_t nblk, const uint32_t *__restrict__ pile_start)
 {
-    __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_carry;
+    __shared__ uint32_t s_warp[32][5];
+    __shared__ uint32_t s_carry[5];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    for (int k = 0; k < 5; k++) {
-        if (tid == 0) s_carry = pile_start[k];
-        __syncthreads();
-        for (uint32_t base = 0; base < nblk; base += 1024) {
-            uint32_t i = base + tid;
-            uint32_t v = i < nblk ? blk_counts[(size_t)i * 8 + k] : 0, x = v;
+    if (tid < 5) s_carry[tid] = pile_start[tid];
+    __syncthreads();
+    for (uint32_t base = 0; base < nblk; base += 1024) {
+        const uint32_t i = base + tid;
+        uint32_t v[5], x[5];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
-            if (lane == 31) s_warp[w] = x;
-            __syncthreads();
-            uint32_t add = 0;
-            for (int j = 0; j < w; j++) add += s_warp[j];
-            uint32_t carry = s_carry;
-            if (i < nblk) blk_counts[(size_t)i * 8 + k] = carry + add + x - v;
-            __syncthreads();
-            if (tid == 1023) s_carry = carry + add + x;
-            __syncthreads();
+        for (int k = 0; k < 5; k++) {
+            v[k] = i < nblk ? blk_counts[(size_t)i * 8 + k] : 0u;
+            x[k] = v[k];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x[k], o); if (lane >= o) x[k] += y; }
+            if (lane == 31) s_warp[w][k] = x[k];
         }
+        __syncthreads();
+        uint32_t tot[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+            uint32_t add = 0;
+            for (int j = 0; j < w; j++) add += s_warp[j][k];
+            tot[k] = s_carry[k] + add + x[k];
+            if (i < nblk) blk_counts[(size_t)i * 8 + k] = tot[k] - v[k];
+        }
+        __syncthreads();
+        if (tid == 1023) {
+#pragma unroll
+            for (int k = 0; k < 5; k++) s_carry[k] = tot[k];
+        }
+        __syncthreads();
     }
 }
 

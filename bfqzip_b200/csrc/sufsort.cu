@@ -145,7 +145,10 @@ pack3_kernel(const uint8_t *__restrict__ T8, uint64_t n, uint64_t ngroups, uint6
 // GT_S = GT_T + GT_E slots; a group that does not end inside the staged window is DEFERRED: its
 // start is appended to a list and the host runs one more level on those groups with the next
 // symbols as key (MSD recursion; at most ceil(max_len / 14) levels, only repeats get there).
-constexpr int GT_THREADS = 256;
+#ifndef GT_THREADS_N
+#define GT_THREADS_N 256
+#endif
+constexpr int GT_THREADS = GT_THREADS_N;
 #ifndef GT_T_ROWS
 #define GT_T_ROWS 1024
 #endif
@@ -565,7 +568,7 @@ __device__ __forceinline__ void order_group_smem(uint32_t gs, uint32_t len, int 
 }
 
 template <typename K, typename P>
-__global__ void __launch_bounds__(GT_THREADS, 5)
+__global__ void __launch_bounds__(GT_THREADS, 1280 / GT_THREADS)
 group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
