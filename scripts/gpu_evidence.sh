@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-1i evidence: parity tests, both bench arms, ncu launch list, one --set full capture of the hot kernels
+# round-1 evidence (latest: r1j): parity tests, both bench arms, ncu launch list, one --set full capture of the hot kernels
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
 tail -2 gpurun_out/pytest_gpu.log
@@ -11,5 +11,5 @@ ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpuru
 python scripts/prof_step.py --steps 1 > gpurun_out/ncu_plain.log 2>&1 &&
 ncu --set full --clock-control none --import-source on \
     -k regex:'group_tile_kernel|rs_onesweep_kernel|walk_kernel|cluster_tile_kernel|rs_suffix_keys_kernel|pack_reads_kernel|pack3_kernel|rank_' \
-    -c 16 -f -o gpurun_out/prof_r1i_all python scripts/prof_step.py --steps 1 > gpurun_out/ncu_all.log 2>&1
+    -c 16 -f -o gpurun_out/prof_r1j_all python scripts/prof_step.py --steps 1 > gpurun_out/ncu_all.log 2>&1
 tail -1 gpurun_out/ncu_all.log | cut -c1-200; ls -la gpurun_out/*.ncu-rep
