@@ -277,8 +277,8 @@ def gpu_arm(args):
                  "keys": "rs_suffix_keys_kernel", "group": "group_tile_kernel", "defer": "defer_*_kernel", "hist": "hist256_kernel",
                  "rank": "rank_*_kernel", "cluster": "cluster_tile_kernel", "cluster_long": "cluster_long_kernel",
                  "rule11": "rule11_kernel", "walk": "walk_kernel", "assemble": "assemble_kernel"}
-        # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1i_hot_kernels.txt), where captured
-        TRAFFIC = {"group": 1544.0e6, "radix_pass": 2409.5e6, "cluster": 714.5e6, "keys": 1394.3e6, "walk": 9252.2e6}
+        # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1j_hot_kernels.txt), where captured
+        TRAFFIC = {"group": 1552.7e6, "radix_pass": 2409.5e6, "cluster": 711.7e6, "keys": 1393.9e6, "walk": 9263.5e6}
         roof_all = {}
         for k, (k_ms, k_n, k_bytes) in prof.items():
             if k_ms > 0 and k_n:
