@@ -1,0 +1,59 @@
+#!/usr/bin/env python
+"""Randomised parity sweep on a GPU box: the fused pipeline against the oracle over coverages, read lengths, error
+rates, variable lengths, modes and the group-ordering options (batched / per-group, flat / walk).  Test infrastructure:
+it calls the oracle as the checker, like tests/ do.
+
+    python scripts/stress_parity.py [--cases 24] [--seed 1]
+"""
+import argparse
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", type=int, default=24)
+    ap.add_argument("--seed", type=int, default=1)
+    a = ap.parse_args()
+    import helpers as H
+    from bfqzip_b200 import lib, synth
+
+    rng = np.random.default_rng(a.seed)
+    ctxs = {}
+    bad = 0
+    for case in range(a.cases):
+        M, B = int(rng.integers(0, 4)), int(rng.integers(0, 2))
+        cov = float(rng.choice([2, 3, 5, 8, 15, 40, 70]))
+        L = int(rng.choice([30, 75, 100, 150, 250]))
+        nreads = int(rng.integers(2000, 9000))
+        err = float(rng.choice([0.0, 0.01, 0.05]))
+        var_len = bool(rng.integers(0, 2))
+        opts = {"batch_min_groups": int(rng.choice([0, 64, 1 << 20])), "rebuild": int(rng.choice([0, 1, 2]))}
+        bases, quals, off = synth.make_reads(nreads, L, 1000 + case, coverage=cov, err=err, var_len=var_len)
+        if (M, B) not in ctxs:
+            ctxs[(M, B)] = lib.BfqGpu(M, B, 0)
+        g = ctxs[(M, B)]
+        for k, v in opts.items():
+            g.set_option(k, v)
+        P = lib.default_params(eos=35)
+        (bwt, qs, lcp), (ob, oq), st = g.pipeline(bases, quals, off, P)
+        rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+        ok_a = np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+        eb, eq, eoff, est, _, _, e = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B))
+        ok_c = e == 0 and np.array_equal(ob, eb) and np.array_equal(oq, eq) and all(
+            st[k] == est[k] for k in ("clusters", "discarded", "ambiguous", "processed", "bases_inside", "qs_smoothed", "modified"))
+        print(f"case {case}: M={M} B={B} cov={cov} L={L} reads={nreads} err={err} var_len={var_len} {opts} "
+              f"partA={'ok' if ok_a else 'DIFF'} partBC={'ok' if ok_c else 'DIFF'}", flush=True)
+        bad += (not ok_a) + (not ok_c)
+    print("stress_parity:", "all ok" if bad == 0 else f"{bad} differences")
+    sys.exit(1 if bad else 0)
+
+
+if __name__ == "__main__":
+    main()
