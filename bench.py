@@ -53,7 +53,31 @@ class ClockSampler(threading.Thread):
         self.stop_evt = threading.Event()
         self.rows = []
 
+    def _run_nvml(self):
+        """NVML from this process: a sample every 2 ms, so that even a 60 ms timed region is covered by dozens."""
+        import pynvml
+        import torch
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+        h = pynvml.nvmlDeviceGetHandleByUUID((uuid if uuid.startswith("GPU-") else "GPU-" + uuid).encode())
+        mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+        bits = ((0x8, 2), (0x40, 3), (0x20, 4), (0x4, 5))      # hw_slowdown, hw_thermal, sw_thermal, sw_power_cap -> row column
+        get = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_evt.is_set():
+            sm = pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            r = int(get(h))
+            row = [str(sm), str(mx), "", "", "", ""]
+            for bit, col in bits:
+                row[col] = "Active" if r & bit else "Not Active"
+            self.rows.append(row)
+            self.stop_evt.wait(0.002)
+
     def run(self):
+        try:
+            self._run_nvml()
+            return
+        except Exception as e:
+            print(f"bench.py: NVML clock sampling unavailable ({type(e).__name__}: {e}); falling back to nvidia-smi", file=sys.stderr)
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         while not self.stop_evt.is_set():
