@@ -252,7 +252,7 @@ def gpu_arm(args):
     ms = e0.elapsed_time(e1)
     launches = g.launch_count() - l0
     prof = {k: g.prof_get(k) for k in ("radix_pass", "radix_hist", "pack", "keys", "group", "defer", "hist", "rank",
-                                        "cluster", "cluster_long", "rule11", "walk", "assemble")}
+                                        "cluster", "cluster_long", "rule11", "walk", "assemble", "unpermute")}
 
     # ---- e2e: host pinned buffers through bfq_pipeline (H2D + D2H inside the timing)
     g.set_option("profile", 0)
@@ -300,7 +300,8 @@ def gpu_arm(args):
         KNAME = {"radix_pass": "rs_onesweep_kernel", "radix_hist": "rs_hist_kernel", "pack": "pack_reads_kernel+pack3_kernel",
                  "keys": "rs_suffix_keys_kernel", "group": "group_tile_kernel", "defer": "defer_*_kernel", "hist": "hist256_kernel",
                  "rank": "rank_*_kernel", "cluster": "cluster_tile_kernel", "cluster_long": "cluster_long_kernel",
-                 "rule11": "rule11_kernel", "walk": "walk_kernel", "assemble": "assemble_kernel"}
+                 "rule11": "rule11_kernel", "walk": "walk_kernel", "assemble": "assemble_kernel / compact_reads_kernel",
+                 "unpermute": "rs_onesweep_kernel<u32,u16> + rs_place_kernel"}
         # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1j_hot_kernels.txt), where captured
         TRAFFIC = {"group": 1552.7e6, "radix_pass": 2409.5e6, "cluster": 711.7e6, "keys": 1393.9e6, "walk": 9263.5e6}
         roof_all = {}

@@ -103,7 +103,10 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     if (!d_lcp) d_lcp = arena_alloc<uint8_t>(c, N + 64);
     // Flat mode (no walk lines, no LF walk): the group kernel also writes the suffix array and the packed text is
     // kept, so part B reads neighbours from the text and part C is a streaming sort back into text order.
-    const bool flat = mx <= (uint64_t)P->max_len && (c->opt_rebuild == 1 || (c->opt_rebuild == 0 && N >= (uint64_t)c->opt_flat_min_rows));
+    // auto: from flat_min_rows rows on; a device-resident call (no host sink: nothing leaves while the walk runs, so the walk's
+    // overlap with the copies does not count) already from flat_min_rows_dev on, where the walk lines outgrow L2
+    const uint64_t auto_min = (uint64_t)(c->sink ? c->opt_flat_min_rows : std::min(c->opt_flat_min_rows, c->opt_flat_min_rows_dev));
+    const bool flat = mx <= (uint64_t)P->max_len && (c->opt_rebuild == 1 || (c->opt_rebuild == 0 && N >= auto_min));
     uint32_t *d_sa = flat ? arena_alloc<uint32_t>(c, N + 16) : nullptr;
     uint64_t *d_t3 = flat ? arena_alloc<uint64_t>(c, packed_text_words(N)) : nullptr;
     {

@@ -42,11 +42,11 @@ struct Error { int code; };   // thrown inside the library, caught at the C ABI
 // ---------------------------------------------------------------- profiling classes
 enum ProfClass {
     PC_RADIX_PASS = 0, PC_RADIX_HIST, PC_PACK, PC_KEYS, PC_GROUP, PC_DEFER, PC_HIST, PC_RANK,
-    PC_CLUSTER, PC_CLUSTER_LONG, PC_RULE11, PC_WALK, PC_ASSEMBLE, PC_COUNT
+    PC_CLUSTER, PC_CLUSTER_LONG, PC_RULE11, PC_WALK, PC_ASSEMBLE, PC_UNPERMUTE, PC_COUNT
 };
 static const char *const kProfNames[PC_COUNT] = {
     "radix_pass", "radix_hist", "pack", "keys", "group", "defer", "hist", "rank",
-    "cluster", "cluster_long", "rule11", "walk", "assemble"};
+    "cluster", "cluster_long", "rule11", "walk", "assemble", "unpermute"};   // unpermute: the passes of the flat-mode rebuild sort
 
 struct ProfEntry {
     double ms = 0; uint64_t launches = 0; uint64_t bytes = 0;
@@ -186,6 +186,7 @@ struct bfq_ctx {
     int64_t opt_batch_min_groups = 64;    // group_tile_kernel: tiles with more groups than this order them in batches
     int opt_rebuild = 0;                  // fused pipeline, part C: 0 auto, 1 streaming un-permute (flat), 2 inverse-LF walk
     int64_t opt_flat_min_rows = 1 << 28;  // auto: flat mode from this many rows on
+    int64_t opt_flat_min_rows_dev = 1 << 26;   // the same for device-resident calls (bfq_pipeline_dev)
     int opt_profile = 0;
     // accounting
     uint64_t launches = 0;

@@ -323,7 +323,7 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 // the passes, given the (unscanned) digit histograms of all of them
 template <typename K, typename V, int ITEMS>
 static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, uint64_t n,
-                        const RsPasses &P, uint32_t *hist, const PermSource *src = nullptr)
+                        const RsPasses &P, uint32_t *hist, const PermSource *src = nullptr, ProfClass cls = PC_RADIX_PASS)
 {
     constexpr int TILE = RS_THREADS * ITEMS;
     const uint32_t tiles = div_up(n, TILE);
@@ -344,7 +344,7 @@ static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, 
     for (int p = 0; p < P.num; p++) {
         BFQ_CUDA(cudaMemsetAsync(status, 0, status_bytes, c->stream));
         {
-            ProfScope ps(c, PC_RADIX_PASS, 2 * n * (sizeof(K) + sizeof(V)));
+            ProfScope ps(c, cls, 2 * n * (sizeof(K) + sizeof(V)));
             const size_t dyn = (size_t)TILE * sizeof(K);
             if constexpr (sizeof(K) == 4 && sizeof(V) == 2) {
                 if (src && p == 0) {
@@ -677,12 +677,12 @@ int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint1
             for (uint32_t d = 0; d < (1u << P.bits[p]); d++) h[p * RS_RADIX + d] = count_digit(n, P.shift[p], P.bits[p], d);
         // pageable source: the copy is staged by the runtime before the call returns
         BFQ_CUDA(cudaMemcpyAsync(hist, h.data(), h.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
-        flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist, src);
+        flip = radix_passes<uint32_t, uint16_t, 16>(c, keys_a, keys_b, vals_a, vals_b, n, P, hist, src, PC_UNPERMUTE);
     }
     if (low) {
         const size_t smem = sizeof(uint16_t) << PL_BITS;
         BFQ_CUDA(cudaFuncSetAttribute(rs_place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ProfScope ps(c, PC_RADIX_PASS, n * (4 + 2 + 2));
+        ProfScope ps(c, PC_UNPERMUTE, n * (4 + 2 + 2));
         rs_place_kernel<<<div_up(n, (uint64_t)1 << PL_BITS), PL_THREADS, smem, c->stream>>>(
             flip ? keys_b : keys_a, flip ? vals_b : vals_a, (uint32_t)n, flip ? vals_a : vals_b);
         BFQ_CUDA(cudaGetLastError());

@@ -40,7 +40,7 @@ def lib_path(M: int, B: int) -> str:
 
 
 PROF_CLASSES = ("radix_pass", "radix_hist", "pack", "keys", "group", "defer", "hist", "rank",
-                "cluster", "cluster_long", "rule11", "walk", "assemble")
+                "cluster", "cluster_long", "rule11", "walk", "assemble", "unpermute")
 
 _libs = {}
 

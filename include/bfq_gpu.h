@@ -84,6 +84,8 @@ void bfq_ctx_destroy(bfq_ctx *ctx);
  *                 group) is ordered in batches of whole groups, one warp per batch, instead of one warp per group; 0 = always
  *   "rebuild"     part C of the fused pipeline: 0 auto, 1 streaming un-permute through the suffix array, 2 inverse-LF walk
  *   "flat_min_rows" auto mode switches to the un-permute from this many BWT rows on
+ *   "flat_min_rows_dev" the same threshold for device-resident calls (bfq_pipeline_dev), default 2^26: with nothing to copy out
+ *                 while part C runs, the un-permute wins as soon as the walk lines outgrow L2
  *   "long_cluster" clusters longer than this many rows go to the block-per-cluster kernel
  *   "profile"     1 = record CUDA events around every kernel class (see bfq_prof_get)
  *   "host_slices" host-buffer calls (bfq_pipeline) launch the group kernel in this many slices and
@@ -183,7 +185,7 @@ int bfq_export_rows(bfq_ctx *ctx, uint8_t *qs_out, uint8_t *obwt_out);
 
 /* Profile counters, filled when option "profile"=1.  Classes: "radix_pass", "radix_hist",
  * "pack", "keys", "group", "defer", "hist", "rank", "cluster", "cluster_long", "rule11",
- * "walk", "assemble".  Returns accumulated device ms, launch count and algorithmic bytes
+ * "walk", "assemble", "unpermute" (the sort passes of the flat-mode rebuild).  Returns accumulated device ms, launch count and algorithmic bytes
  * since bfq_prof_reset.  Unknown class -> BFQ_EINVAL. */
 int  bfq_prof_get(bfq_ctx *ctx, const char *klass, double *ms, uint64_t *launches, uint64_t *bytes);
 void bfq_prof_reset(bfq_ctx *ctx);
