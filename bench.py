@@ -302,8 +302,9 @@ def gpu_arm(args):
                  "rank": "rank_*_kernel", "cluster": "cluster_tile_kernel", "cluster_long": "cluster_long_kernel",
                  "rule11": "rule11_kernel", "walk": "walk_kernel", "assemble": "assemble_kernel / compact_reads_kernel",
                  "unpermute": "rs_onesweep_kernel<u32,u16> + rs_place_kernel"}
-        # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1j_hot_kernels.txt), where captured
-        TRAFFIC = {"group": 1552.7e6, "radix_pass": 2409.5e6, "cluster": 711.7e6, "keys": 1393.9e6, "walk": 9263.5e6}
+        # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1k_hot_kernels.txt: the device-resident step,
+        # flat mode -- the group kernel also writes the suffix array, the cluster kernel one stored-quality byte per row)
+        TRAFFIC = {"group": 1948.5e6, "radix_pass": 2409.5e6, "cluster": 417.8e6, "keys": 1393.9e6}
         roof_all = {}
         for k, (k_ms, k_n, k_bytes) in prof.items():
             if k_ms > 0 and k_n:
