@@ -10,16 +10,18 @@
 // The compile-time modes of the reference (-DM=0..3, -DB=0|1, src_ext_mem/makefile:10-22) are
 // compile-time here too: BFQ_M / BFQ_B.
 //
-// HBM layout.  One 64-byte WALK LINE per 32 BWT rows:
-//     u32 cnt[5]   occurrences of codes 1..5 in rows [0, 32*line) PLUS the pile start C[code]
-//                  (so LF(row) = cnt[c-1] + popc(match(c) & below(row)) is one line fetch)
-//     u32 plane[3] bit b of the 3-bit code of each of the 32 rows (row r = bit r)
-//     u8  q[32]    stored quality of each row (smoothed, binned when B=1); bit 7 set when the
+// HBM layout (see ws_load in common.cuh).  One 32-byte WALK SECTOR per 16 BWT rows:
+//     u16 rel[5]   occurrences of codes 1..5 in the rows of this super-block (8192 rows) before the sector
+//     u16 plane[3] bit b of the 3-bit code of each of the 16 rows (row r = bit r)
+//     u8  q[16]    stored quality of each row (smoothed, binned when B=1); bit 7 set when the
 //                  output base differs from the BWT symbol (then obase[row] holds it)
-// so one inverse-LF step (part C) touches exactly one aligned 64-byte line.
+// plus u32[8] per super-block (absolute occurrences before it + pile start C[code]; cache resident), so one
+// inverse-LF step (part C) touches exactly one aligned 32-byte DRAM sector.  Flat mode (fused pipeline with the
+// suffix array at hand) builds no sectors at all: the stored qualities are a plain per-row array.
 #include "common.cuh"
 #include <math.h>
 #include <algorithm>
+#include <mutex>
 
 namespace bfq {
 
@@ -38,9 +40,12 @@ struct SmoothConst {
     uint8_t nsym;
     uint32_t long_len;
 };
-__constant__ SmoothConst g_sc;
+// SmoothConst travels as a kernel argument (__grid_constant__): it depends on the call (flags, alphabet of THIS
+// collection), and several contexts may run on one device.  The two M=1 tables are pure functions of nothing: they
+// are module constants, written once per device.
 __constant__ double g_errtab[256];     // pow(10, -(q-33)/10), host glibc (bfq_ext.cpp:532)
 __constant__ double g_m1thr[128];      // g_m1thr[v] = largest x with round(-10*log10(x)) >= v
+#define SC_ARG const __grid_constant__ SmoothConst g_sc
 
 // decode.cpp:72-84 on an ASCII quality (the caller's `foundQual-33` wraps in uchar like the reference)
 __device__ __forceinline__ uint8_t bin8(uint8_t ascii)
@@ -105,7 +110,7 @@ __device__ __forceinline__ void load_group_codes(const uint8_t *__restrict__ bwt
 }
 
 __global__ void __launch_bounds__(RK_THREADS)
-rank_count_kernel(const uint8_t *__restrict__ bwt, uint64_t n, uint32_t *__restrict__ blk_counts)
+rank_count_kernel(SC_ARG, const uint8_t *__restrict__ bwt, uint64_t n, uint32_t *__restrict__ blk_counts)
 {
     __shared__ uint8_t s_lut[256];
     __shared__ uint32_t s_cnt[5];
@@ -164,7 +169,7 @@ rank_scan_kernel(uint32_t *__restrict__ blk_counts, uint32_t nblk, const uint32_
 }
 
 __global__ void __launch_bounds__(RK_THREADS)
-rank_build_kernel(const uint8_t *__restrict__ bwt, uint64_t n, uint8_t *__restrict__ lines)
+rank_build_kernel(SC_ARG, const uint8_t *__restrict__ bwt, uint64_t n, uint8_t *__restrict__ lines)
 {
     __shared__ uint8_t s_lut[256];
     __shared__ uint32_t s_warp[RK_THREADS / 32][5];
@@ -226,7 +231,7 @@ struct ClAcc {                     // per-cluster accumulators (rule 8, bfq_ext.
 enum { ACT_NONE = 0, ACT_RULE10 = 1, ACT_RULE11 = 2 };
 struct Decision { int act; uint32_t sym, f0, f1; uint8_t newqs; };
 
-__device__ __forceinline__ uint8_t newqs_from(const ClAcc &a)
+__device__ __forceinline__ uint8_t newqs_from(const SmoothConst &g_sc, const ClAcc &a)
 {
 #if BFQ_M == 0
     return (uint8_t)a.mx;                                            // bfq_ext.cpp:502-518
@@ -246,14 +251,14 @@ __device__ __forceinline__ uint8_t newqs_from(const ClAcc &a)
 }
 
 // rules 7-9 (bfq_ext.cpp:584, 633, 665-713).  st[] are this thread's counters.
-__device__ __forceinline__ Decision decide(uint32_t len, const ClAcc &a, uint32_t *st)
+__device__ __forceinline__ Decision decide(const SmoothConst &g_sc, uint32_t len, const ClAcc &a, uint32_t *st)
 {
     Decision d{ACT_NONE, 0, 0, 0, 0};
     if ((int)len < g_sc.m) return d;
     if (a.base_num == 0) return d;
     st[ST_CLUSTERS]++;
     st[ST_BASES] += a.base_num;
-    d.newqs = newqs_from(a);
+    d.newqs = newqs_from(g_sc, a);
     uint32_t F[3]; int nF = 0;
 #pragma unroll
     for (uint32_t c = 1; c <= 5; c++) {
@@ -286,7 +291,7 @@ __device__ __forceinline__ uint8_t rule10_row(uint32_t c, uint8_t q, uint32_t sy
     return q;
 }
 
-__device__ __forceinline__ void acc_row(ClAcc &a, uint32_t c, uint8_t q)
+__device__ __forceinline__ void acc_row(const SmoothConst &g_sc, ClAcc &a, uint32_t c, uint8_t q)
 {
     if (c == 0) return;
     a.freq[c]++;
@@ -302,7 +307,7 @@ __device__ __forceinline__ void acc_row(ClAcc &a, uint32_t c, uint8_t q)
 }
 
 // rule 5-6 flag of row i (bfq_ext.cpp:375-392, 880): lcp[i] >= K and row i is not a local minimum
-__device__ __forceinline__ bool f_flag(int lm1, int l0, int lp1, bool is_first, bool is_last)
+__device__ __forceinline__ bool f_flag(const SmoothConst &g_sc, int lm1, int l0, int lp1, bool is_first, bool is_last)
 {
     if (is_first) return false;
     bool thr = l0 >= g_sc.K;
@@ -319,28 +324,41 @@ struct SmoothLists {
 };
 
 // ------------------------------------------------------------------ tile kernel (rules 5-10)
-// One block stages CL_TILE rows of bwt/qs/lcp in shared memory, finds the clusters that START
-// in the tile, and one thread walks each cluster (cluster lengths are ~5-40 rows; clusters longer
-// than g_sc.long_len rows go to cluster_long_kernel, two-base clusters to rule11_kernel).
-// A tile writes the stored quality of every row it owns: all rows except its leading run of
-// flagged rows (those belong to a cluster that started in an earlier tile, whose owner writes them).
-constexpr int CL_THREADS = 256;
-#ifndef CLT_THREADS_N
-#define CLT_THREADS_N 128
-#endif
-constexpr int CLT_THREADS = CLT_THREADS_N;   // tile kernel: a tile holds ~120 clusters, one thread each
+// Row-parallel: one block stages CL_S = CL_TILE + CL_EXT rows, 16 consecutive rows per thread, and keeps them in
+// registers from the loads to the stores.
+//   1. 16-byte loads of bwt / qs / lcp; codes through the LUT; the rule 5-6 flag of every row from the 3-point LCP
+//      stencil (the LCP itself is not kept); the thread's rows as bit planes (code bits, "quality >= qthr").
+//   2. A cluster is an unflagged row followed by a maximal run of flagged rows.  Cluster starts are the bit pattern
+//      ~f & (f >> 1); their block-wide exclusive count (warp scan + warp totals) numbers the clusters of the window, so
+//      every row knows its cluster's ORDINAL without searching.
+//   3. Segmented reduction of the rule-8 statistics: a thread cuts its 16 rows into segments at the cluster ends,
+//      gets the per-symbol row counts and "has a high quality" counts of a segment from popcounts on the bit planes,
+//      and adds them to its cluster's accumulator in shared memory (a cluster spans 2-4 threads at 40x coverage).
+//   4. One thread per cluster: length from the flag bitmap, rule 9 decision, statistics, hand-over of clusters that
+//      leave the window / exceed long_len (cluster_long_kernel) and of two-base clusters (rule11_kernel).  M=1 sums
+//      the error probabilities here, serially in row order (double addition is not associative, bfq_ext.cpp:522-543).
+//   5. Rule 10 row by row in registers with the decision of the row's cluster; the stored qualities leave as one
+//      16-byte store per thread (= the quality half of one walk sector).
+// A tile owns the rows [t0, t0 + CL_TILE) except its leading run of flagged rows (they belong to a cluster that
+// started in an earlier tile, whose block writes them from its staged extension) plus the rows of its own last
+// cluster that lie past the tile.  More than CL_CAP clusters in a window (tiny -k) are processed in rounds.
+constexpr int CL_THREADS = 256;             // cluster_long_kernel
+constexpr int CLT_THREADS = 288;            // tile kernel: one 16-row chunk per thread
 constexpr int CL_TILE = 4096;
 constexpr int CL_EXT = 512;                 // rows staged past the tile: a cluster that starts in the tile and ends inside
 constexpr int CL_S = CL_TILE + CL_EXT;      // the staged window is finished here, longer ones go to cluster_long_kernel
+constexpr int CL_CHUNKS = CL_S / 16;
+constexpr int CL_CAP = 1024;                // cluster accumulators per round
+constexpr int CL_ACCW = 5;                  // words per accumulator: 11 counters of 10 bits + the M=0 / M=3 word
+constexpr uint32_t CL_LONG_MAX = 1023;      // 10-bit counters: longer clusters always go to cluster_long_kernel
+static_assert(CLT_THREADS == CL_CHUNKS, "one chunk per thread");
 
 __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stats, unsigned long long *g_stats)
 {
     // caller zeroed s_stats and synchronised before; all threads of the block call this
 #pragma unroll
     for (int k = 0; k < ST_COUNT; k++) {
-        uint32_t v = st[k];
-#pragma unroll
-        for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        const uint32_t v = __reduce_add_sync(0xffffffffu, st[k]);
         if ((threadIdx.x & 31) == 0 && v) atomicAdd(&s_stats[k], v);
     }
     __syncthreads();
@@ -348,54 +366,61 @@ __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stat
         atomicAdd(&g_stats[threadIdx.x], (unsigned long long)s_stats[threadIdx.x]);
 }
 
+// bit 0 of each of the four bytes of x -> bits 0..3
+__device__ __forceinline__ uint32_t gather_bit0(uint32_t x) { return ((x & 0x01010101u) * 0x01020408u) >> 24; }
+
 template <bool FLAT>
-__global__ void __launch_bounds__(CLT_THREADS, 1536 / CLT_THREADS)
-cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
+__global__ void __launch_bounds__(CLT_THREADS, 4)
+cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
                     uint8_t *__restrict__ obase, SmoothLists L)
 {
-    __shared__ __align__(16) uint8_t s_code[CL_S + 16];
-    __shared__ __align__(16) uint8_t s_q[CL_S + 16];
-    __shared__ __align__(16) uint8_t s_f[CL_S + 16];   // rule 5-6 flag of every staged row (+ one past the window)
-    __shared__ uint16_t s_starts[CL_TILE / 2 + 2];
-    __shared__ uint32_t s_nstarts, s_lead;
-    __shared__ uint8_t s_lut[256];
+    __shared__ uint32_t s_acc[CL_CAP * CL_ACCW];
+    __shared__ uint32_t s_dec[CL_CAP];          // bit 0 rule 10, bit 1 "closed here: its rows past the tile are mine", sym << 4, hiq << 8, newqs << 16
+    __shared__ uint16_t s_start[CL_S / 2 + 2];  // window row of every cluster start, by ordinal
+    __shared__ uint32_t s_fb[CL_CHUNKS + 1];    // flags of chunk k in bits 0..15; [CL_CHUNKS] bit 0 = flag of row CL_S
+    __shared__ uint32_t s_wsum[CLT_THREADS / 32];
     __shared__ uint32_t s_stats[ST_COUNT];
-
-    const int tid = threadIdx.x;
+    __shared__ uint8_t s_lut[256];
+#if BFQ_M == 1
+    __shared__ __align__(16) uint8_t s_code[CL_S], s_q[CL_S];
+#endif
+    const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
     const int64_t t0 = (int64_t)blockIdx.x * CL_TILE;
     const int64_t nn = (int64_t)n;
     for (int i = tid; i < 256; i += CLT_THREADS) s_lut[i] = g_sc.byte2code[i];
-    if (tid == 0) { s_nstarts = 0; s_lead = CL_TILE; }
     if (tid < ST_COUNT) s_stats[tid] = 0;
     __syncthreads();
-    // ---- staging, 16 rows per thread and step: codes, qualities and the rule 5-6 flags (3-point stencil on the LCP,
-    // computed in registers: the LCP itself is not kept).  Chunk CL_S / 16 only supplies the flag of row t0 + CL_S.
+
+    // ---- 1. this thread's 16 rows
+    const int r0 = 16 * tid;
+    const int64_t i0 = t0 + r0;
+    uint32_t wl[4] = {0, 0, 0, 0}, cw[4] = {0, 0, 0, 0}, qw[4] = {0, 0, 0, 0};     // 16 packed bytes each
     const bool vec = ((reinterpret_cast<uintptr_t>(bwt) | reinterpret_cast<uintptr_t>(qs) | reinterpret_cast<uintptr_t>(lcp)) & 15) == 0;
-    for (int k = tid; k <= CL_S / 16; k += CLT_THREADS) {
-        const int r0 = 16 * k;
-        const int64_t i0 = t0 + r0;
-        uint32_t wl[4] = {0, 0, 0, 0}, cw[4] = {0, 0, 0, 0}, qw[4] = {0, 0, 0, 0}, fw[4] = {0, 0, 0, 0};     // 16 packed bytes each
-        if (vec && i0 + 16 <= nn) {
-            const uint4 vl = *reinterpret_cast<const uint4 *>(lcp + i0);
-            const uint4 vb = *reinterpret_cast<const uint4 *>(bwt + i0);
-            const uint4 vq = *reinterpret_cast<const uint4 *>(qs + i0);
-            wl[0] = vl.x; wl[1] = vl.y; wl[2] = vl.z; wl[3] = vl.w;
-            qw[0] = vq.x; qw[1] = vq.y; qw[2] = vq.z; qw[3] = vq.w;
-            const uint32_t wb[4] = {vb.x, vb.y, vb.z, vb.w};
+    const bool full = i0 + 16 <= nn;
+    if (vec && full) {
+        const uint4 vl = *reinterpret_cast<const uint4 *>(lcp + i0);
+        const uint4 vb = *reinterpret_cast<const uint4 *>(bwt + i0);
+        const uint4 vq = *reinterpret_cast<const uint4 *>(qs + i0);
+        wl[0] = vl.x; wl[1] = vl.y; wl[2] = vl.z; wl[3] = vl.w;
+        qw[0] = vq.x; qw[1] = vq.y; qw[2] = vq.z; qw[3] = vq.w;
+        const uint32_t wb[4] = {vb.x, vb.y, vb.z, vb.w};
 #pragma unroll
-            for (int j = 0; j < 16; j++) cw[j >> 2] |= (uint32_t)s_lut[(wb[j >> 2] >> (8 * (j & 3))) & 255u] << (8 * (j & 3));
-        } else {
+        for (int j = 0; j < 16; j++) cw[j >> 2] |= (uint32_t)s_lut[(wb[j >> 2] >> (8 * (j & 3))) & 255u] << (8 * (j & 3));
+    } else {
 #pragma unroll
-            for (int j = 0; j < 16; j++) {
-                const int64_t i = i0 + j;
-                if (i < nn) {
-                    wl[j >> 2] |= (uint32_t)lcp[i] << (8 * (j & 3));
-                    cw[j >> 2] |= (uint32_t)s_lut[bwt[i]] << (8 * (j & 3));
-                    qw[j >> 2] |= (uint32_t)qs[i] << (8 * (j & 3));
-                }
+        for (int j = 0; j < 16; j++) {
+            const int64_t i = i0 + j;
+            if (i < nn) {
+                wl[j >> 2] |= (uint32_t)lcp[i] << (8 * (j & 3));
+                cw[j >> 2] |= (uint32_t)s_lut[bwt[i]] << (8 * (j & 3));
+                qw[j >> 2] |= (uint32_t)qs[i] << (8 * (j & 3));
             }
         }
+    }
+    const uint32_t valid = full ? 0xFFFFu : (i0 < nn ? (1u << (nn - i0)) - 1u : 0u);          // rows of the chunk inside the BWT
+    uint32_t f16 = 0;
+    {
         const uint32_t lprev = (i0 > 0 && i0 - 1 < nn) ? lcp[i0 - 1] : 0u, lnext = (i0 + 16 < nn) ? lcp[i0 + 16] : 0u;
 #pragma unroll
         for (int j = 0; j < 16; j++) {
@@ -403,115 +428,208 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
             const uint32_t lm = j == 0 ? lprev : (wl[(j - 1) >> 2] >> (8 * ((j - 1) & 3))) & 255u;
             const uint32_t l0 = (wl[j >> 2] >> (8 * (j & 3))) & 255u;
             const uint32_t lp = j == 15 ? lnext : (wl[(j + 1) >> 2] >> (8 * ((j + 1) & 3))) & 255u;
-            const bool f = (i > 0 && i < nn) ? f_flag((int)lm, (int)l0, (int)lp, false, i == nn - 1) : false;
-            fw[j >> 2] |= (uint32_t)f << (8 * (j & 3));
+            const bool f = (i > 0 && i < nn) ? f_flag(g_sc, (int)lm, (int)l0, (int)lp, false, i == nn - 1) : false;
+            f16 |= (uint32_t)f << j;
         }
-        *reinterpret_cast<uint4 *>(s_f + r0) = make_uint4(fw[0], fw[1], fw[2], fw[3]);
-        if (r0 < CL_S) {
-            *reinterpret_cast<uint4 *>(s_code + r0) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
-            *reinterpret_cast<uint4 *>(s_q + r0) = make_uint4(qw[0], qw[1], qw[2], qw[3]);
+    }
+    s_fb[tid] = f16;
+    if (tid == CLT_THREADS - 1) {               // flag of the row just past the window (is the last cluster still open there?)
+        const int64_t i = t0 + CL_S;
+        bool f = false;
+        if (i > 0 && i < nn) f = f_flag(g_sc, (int)lcp[i - 1], (int)lcp[i], i + 1 < nn ? (int)lcp[i + 1] : 0, false, i == nn - 1);
+        s_fb[CL_CHUNKS] = f ? 1u : 0u;
+    }
+#if BFQ_M == 1
+    *reinterpret_cast<uint4 *>(s_code + r0) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
+    *reinterpret_cast<uint4 *>(s_q + r0) = make_uint4(qw[0], qw[1], qw[2], qw[3]);
+#endif
+    // bit planes of the 16 codes and the "quality >= qthr + 33" bits (qualities are < 128: smooth_dev checks)
+    uint32_t p0 = 0, p1 = 0, p2 = 0, hq = 0;
+    {
+        const uint32_t thr4 = (uint32_t)min(max(g_sc.qthr + 33, 0), 128) * 0x01010101u;
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+            p0 |= gather_bit0(cw[w]) << (4 * w);
+            p1 |= gather_bit0(cw[w] >> 1) << (4 * w);
+            p2 |= gather_bit0(cw[w] >> 2) << (4 * w);
+            hq |= gather_bit0((((qw[w] | 0x80808080u) - thr4) & 0x80808080u) >> 7) << (4 * w);
         }
     }
     __syncthreads();
 
-    // ---- cluster starts and the leading run
-    for (int k = tid; k < CL_TILE / 16; k += CLT_THREADS) {
-        const int r0 = 16 * k;
-        if (t0 + r0 >= nn) break;
-        const uint4 v = *reinterpret_cast<const uint4 *>(s_f + r0);
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-        uint32_t m = (uint32_t)s_f[r0 + 16] << 16;                 // bit j = flag of row r0 + j
+    // ---- 2. cluster starts, ordinals
+    const uint32_t f17 = f16 | ((s_fb[tid + 1] & 1u) << 16);
+    const uint32_t startm = ~f16 & (f17 >> 1) & 0xFFFFu;      // an unflagged row followed by a flagged one opens a cluster
+    const uint32_t inm = f16 | startm;                         // rows that belong to some cluster
+    const uint32_t endm = inm & ~(f17 >> 1);                   // last row of its cluster
+    uint32_t ord0, total;
+    {
+        const uint32_t cnt = __popc(startm);
+        uint32_t x = cnt;
 #pragma unroll
-        for (int j = 0; j < 16; j++) m |= ((w[j >> 2] >> (8 * (j & 3))) & 1u) << j;
-        const int64_t left = nn - (t0 + r0);
-        const uint32_t notf = ~m & (left >= 16 ? 0xFFFFu : ((1u << left) - 1u));
-        if (notf) atomicMin(&s_lead, (uint32_t)(r0 + __ffs(notf) - 1));
-        uint32_t starts = notf & (m >> 1);                         // an unflagged row followed by a flagged one opens a cluster
-        while (starts) {
-            const int j = __ffs(starts) - 1;
-            s_starts[atomicAdd(&s_nstarts, 1u)] = (uint16_t)(r0 + j);
-            starts &= starts - 1;
-        }
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+        if (lane == 31) s_wsum[wrp] = x;
+        __syncthreads();
+        uint32_t add = 0, tot = 0;
+#pragma unroll
+        for (int i = 0; i < CLT_THREADS / 32; i++) { const uint32_t v = s_wsum[i]; if (i < wrp) add += v; tot += v; }
+        ord0 = add + x - cnt;                                  // clusters that start before this chunk
+        total = tot;
     }
-    __syncthreads();
-    const uint32_t nstarts = s_nstarts;
+    {
+        uint32_t m = startm, k = ord0;
+        while (m) { s_start[k++] = (uint16_t)(r0 + __ffs(m) - 1); m &= m - 1; }
+    }
+    // rows of this chunk that continue a cluster of an earlier tile (ordinal -1): not mine
+    uint32_t leadm = 0;
+    if (ord0 == 0 && (inm & 1u) && !(startm & 1u)) {
+        const uint32_t sm = startm ? ((1u << (__ffs(startm) - 1)) - 1u) : 0xFFFFu;      // rows before the first start of the window
+        const uint32_t em = endm & sm;
+        leadm = em ? ((2u << (__ffs(em) - 1)) - 1u) : (inm & sm);                          // up to the run's end, or all of them
+        leadm &= inm;
+    }
+
     uint32_t st[ST_COUNT];
 #pragma unroll
     for (int k = 0; k < ST_COUNT; k++) st[k] = 0;
+    uint32_t extm = 0;                                          // rows past the tile that this block writes
+    const uint32_t long_len = min(g_sc.long_len, CL_LONG_MAX);
 
-    for (uint32_t idx = tid; idx < nstarts; idx += CLT_THREADS) {
-        const int a = s_starts[idx];
-        int e = a + 1;
-        while (e <= CL_S && s_f[e]) e++;
-        if (e > CL_S || (uint32_t)(e - a) > g_sc.long_len) {    // open at the end of the window, or too long for one thread: hand over
-            uint32_t k = atomicAdd(L.long_count, 1u);
-            if (k < L.long_cap) L.long_starts[k] = (uint32_t)(t0 + a);
-            continue;
-        }
-        const uint32_t len = (uint32_t)(e - a);
-        // pass 1: statistics (rule 8)
-        unsigned long long fpack = 0;                          // 12-bit counters per code (len <= long_len <= 4000)
-        ClAcc acc;
-        acc.hiq = 0; acc.base_num = 0; acc.mx = 0; acc.isum = 0; acc.dsum = 0.0;
-        for (int r = a; r < e; r++) {
-            const uint32_t c = s_code[r]; const uint8_t q = s_q[r];
-            if (c) {
-                fpack += 1ull << (12 * (c - 1));
-                acc.base_num++;
-                if ((int)q >= g_sc.qthr + 33) acc.hiq |= 1u << c;
-#if BFQ_M == 0
-                acc.mx = max(acc.mx, (uint32_t)q);
-#elif BFQ_M == 1
-                acc.dsum = __dadd_rn(acc.dsum, g_errtab[q]);
-#elif BFQ_M == 3
-                acc.isum += (int32_t)q;
-#endif
+    for (uint32_t base = 0; base < total; base += CL_CAP) {    // (block-uniform; one round unless -k is tiny)
+        const uint32_t cnt = min((uint32_t)CL_CAP, total - base);
+        for (uint32_t i = tid; i < cnt * CL_ACCW; i += CLT_THREADS) s_acc[i] = 0;
+        __syncthreads();
+        // ---- 3. segmented reduction into the cluster accumulators
+        {
+            uint32_t m = inm & ~leadm;
+            while (m) {
+                const int a = __ffs(m) - 1;
+                const uint32_t em = endm >> a;
+                const int slen = em ? __ffs(em) : 16 - a;
+                const uint32_t seg = ((1u << slen) - 1u) << a;
+                m &= ~seg;
+                const uint32_t o = ord0 + __popc(startm & ((2u << a) - 1u)) - 1u - base;
+                if (o < cnt) {
+                    const uint32_t n0 = ~p0 & seg, n1 = ~p1 & seg, n2 = ~p2 & seg;
+                    const uint32_t m0 = n0 & n1 & n2, m1 = p0 & n1 & n2, m2 = n0 & p1 & n2, m3 = p0 & p1 & n2, m4 = n0 & n1 & p2, m5 = p0 & n1 & p2;
+                    uint32_t *acc = s_acc + o * CL_ACCW;
+                    atomicAdd(acc + 0, __popc(m0) | (__popc(m1) << 10) | (__popc(m2) << 20));
+                    atomicAdd(acc + 1, __popc(m3) | (__popc(m4) << 10) | (__popc(m5) << 20));
+                    atomicAdd(acc + 2, __popc(m1 & hq) | (__popc(m2 & hq) << 10) | (__popc(m3 & hq) << 20));
+                    atomicAdd(acc + 3, __popc(m4 & hq) | (__popc(m5 & hq) << 10));
+                }
             }
         }
+#if BFQ_M == 0 || BFQ_M == 3
+        {   // largest quality (M=0) / sum of the qualities (M=3) of the non-EOS rows, per cluster
+            uint32_t cur = ord0 - 1u - base, X = 0;
 #pragma unroll
-        for (int c = 1; c < 6; c++) acc.freq[c] = (uint32_t)(fpack >> (12 * (c - 1))) & 0xFFFu;
-        acc.freq[0] = 0;
-        Decision d = decide(len, acc, st);
-        if (d.act == ACT_RULE11) {
-            uint32_t k = atomicAdd(L.r11_count, 1u);
-            if (k < L.r11_cap)
-                L.r11[k] = R11Desc{(uint32_t)(t0 + a), len, d.f0 | (d.f1 << 8) | ((uint32_t)d.newqs << 16) | (acc.hiq << 24), 0};
+            for (int j = 0; j < 16; j++) {
+                cur += (startm >> j) & 1u;
+                const uint32_t c = (cw[j >> 2] >> (8 * (j & 3))) & 255u, q = (qw[j >> 2] >> (8 * (j & 3))) & 255u;
+                if (((inm >> j) & 1u) && c) {
+#if BFQ_M == 0
+                    X = max(X, q);
+#else
+                    X += q;
+#endif
+                }
+                if (((endm >> j) & 1u) || j == 15) {
+                    if (X && cur < cnt && !((leadm >> j) & 1u)) {
+#if BFQ_M == 0
+                        atomicMax(s_acc + cur * CL_ACCW + 4, X);
+#else
+                        atomicAdd(s_acc + cur * CL_ACCW + 4, X);
+#endif
+                    }
+                    X = 0;
+                }
+            }
         }
-        if (d.act != ACT_RULE10 && e <= CL_TILE) continue;     // nothing changes, all rows inside the tile
-        // pass 2: apply rule 10 / write the rows that lie beyond this tile (the next tile skips them)
-        const uint8_t symb = g_sc.code2byte[d.sym];
-        for (int r = a; r < e; r++) {
-            const uint32_t c = s_code[r]; const uint8_t q = s_q[r];
-            uint8_t o = q;
-            if (d.act == ACT_RULE10) o = rule10_row(c, q, d.sym, acc.hiq, d.newqs, st);
-            if (o & 0x80) obase[t0 + r] = symb;
-            if (r < CL_TILE) { if (o != q) s_q[r] = o; }
-            else *q_slot<FLAT>(lines, (uint64_t)(t0 + r)) = store_q(o);
+#endif
+        __syncthreads();
+        // ---- 4. one thread per cluster: rules 7-9
+        for (uint32_t k = tid; k < cnt; k += CLT_THREADS) {
+            const int a = s_start[base + k];
+            uint32_t dec = 0;
+            if (a < CL_TILE) {                                  // (clusters that start in the extension belong to the next tile)
+                int ch = (a + 1) >> 4;
+                uint32_t bits = ~s_fb[ch] & 0xFFFFu & (0xFFFFu << ((a + 1) & 15));
+                while (!bits) bits = ~s_fb[++ch] & 0xFFFFu;    // s_fb[CL_CHUNKS] has zero bits: terminates
+                const int e = 16 * ch + __ffs(bits) - 1;       // first unflagged row after the start
+                const uint32_t len = (uint32_t)(e - a);
+                if (e > CL_S || len > long_len) {               // open at the end of the window, or too long: hand over
+                    const uint32_t kk = atomicAdd(L.long_count, 1u);
+                    if (kk < L.long_cap) L.long_starts[kk] = (uint32_t)(t0 + a);
+                } else {
+                    dec = 2u;
+                    const uint32_t *acc = s_acc + k * CL_ACCW;
+                    const uint32_t w0 = acc[0], w1 = acc[1], w2 = acc[2], w3 = acc[3];
+                    ClAcc A;
+                    A.freq[0] = 0;
+                    A.freq[1] = (w0 >> 10) & 1023u; A.freq[2] = w0 >> 20;
+                    A.freq[3] = w1 & 1023u; A.freq[4] = (w1 >> 10) & 1023u; A.freq[5] = w1 >> 20;
+                    A.hiq = ((w2 & 1023u) ? 2u : 0u) | (((w2 >> 10) & 1023u) ? 4u : 0u) | ((w2 >> 20) ? 8u : 0u) |
+                            ((w3 & 1023u) ? 16u : 0u) | ((w3 >> 10) ? 32u : 0u);
+                    A.base_num = A.freq[1] + A.freq[2] + A.freq[3] + A.freq[4] + A.freq[5];
+                    A.mx = acc[4]; A.isum = (int32_t)acc[4]; A.dsum = 0.0;
+#if BFQ_M == 1
+                    for (int r = a; r < e; r++) if (s_code[r]) A.dsum = __dadd_rn(A.dsum, g_errtab[s_q[r]]);
+#endif
+                    const Decision d = decide(g_sc, len, A, st);
+                    if (d.act == ACT_RULE11) {
+                        const uint32_t kk = atomicAdd(L.r11_count, 1u);
+                        if (kk < L.r11_cap)
+                            L.r11[kk] = R11Desc{(uint32_t)(t0 + a), len, d.f0 | (d.f1 << 8) | ((uint32_t)d.newqs << 16) | (A.hiq << 24), 0};
+                    } else if (d.act == ACT_RULE10)
+                        dec = 3u | (d.sym << 4) | (A.hiq << 8) | ((uint32_t)d.newqs << 16);
+                }
+            }
+            s_dec[k] = dec;
         }
+        __syncthreads();
+        // ---- 5. rule 10, row by row in registers
+        if (inm & ~leadm) {
+            uint32_t cur = ord0 - 1u - base, dec = 0;
+            if (cur < cnt) dec = s_dec[cur];
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+                if ((startm >> j) & 1u) { cur++; dec = cur < cnt ? s_dec[cur] : 0u; }
+                if (((inm & ~leadm) >> j) & 1u) {
+                    if (r0 + j >= CL_TILE && (dec & 2u)) extm |= 1u << j;
+                    if (dec & 1u) {
+                        const uint32_t c = (cw[j >> 2] >> (8 * (j & 3))) & 255u;
+                        const uint8_t q = (uint8_t)(qw[j >> 2] >> (8 * (j & 3)));
+                        const uint8_t o = rule10_row(c, q, (dec >> 4) & 15u, (dec >> 8) & 255u, (uint8_t)(dec >> 16), st);
+                        if (o != q) {
+                            qw[j >> 2] = (qw[j >> 2] & ~(255u << (8 * (j & 3)))) | ((uint32_t)o << (8 * (j & 3)));
+                            if (o & 0x80) obase[i0 + j] = g_sc.code2byte[(dec >> 4) & 15u];
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
     }
-    __syncthreads();
-    // ---- stored qualities of the rows this tile owns
-    const uint32_t lead = s_lead;
-    for (int k = tid; k < CL_TILE / 16; k += CLT_THREADS) {
-        const int r0 = 16 * k;
-        const int64_t i0 = t0 + r0;
-        if (i0 >= nn || (uint32_t)(r0 + 15) < lead) continue;
+
+    // ---- stored qualities of the rows this block owns
+    const uint32_t own = (r0 < CL_TILE ? (valid & ~leadm) : extm) & valid;
+    if (own) {
         uint8_t *dst = q_slot<FLAT>(lines, (uint64_t)i0);         // 16 rows = the quality half of one walk sector
-        if ((uint32_t)r0 >= lead && i0 + 16 <= nn && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-            const uint4 v = *reinterpret_cast<const uint4 *>(s_q + r0);
-            uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #if BFQ_B
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const uint32_t x = w[j];
-                w[j] = (uint32_t)store_q((uint8_t)x) | ((uint32_t)store_q((uint8_t)(x >> 8)) << 8) |
-                       ((uint32_t)store_q((uint8_t)(x >> 16)) << 16) | ((uint32_t)store_q((uint8_t)(x >> 24)) << 24);
-            }
+        for (int j = 0; j < 4; j++) {
+            const uint32_t x = qw[j];
+            qw[j] = (uint32_t)store_q((uint8_t)x) | ((uint32_t)store_q((uint8_t)(x >> 8)) << 8) |
+                    ((uint32_t)store_q((uint8_t)(x >> 16)) << 16) | ((uint32_t)store_q((uint8_t)(x >> 24)) << 24);
+        }
 #endif
-            *reinterpret_cast<uint4 *>(dst) = make_uint4(w[0], w[1], w[2], w[3]);
-        } else {
+        if (own == 0xFFFFu && (reinterpret_cast<uintptr_t>(dst) & 15) == 0)
+            *reinterpret_cast<uint4 *>(dst) = make_uint4(qw[0], qw[1], qw[2], qw[3]);
+        else {
+#pragma unroll
             for (int j = 0; j < 16; j++)
-                if (i0 + j < nn && (uint32_t)(r0 + j) >= lead) *q_slot<FLAT>(lines, (uint64_t)(i0 + j)) = store_q(s_q[r0 + j]);
+                if ((own >> j) & 1u) *q_slot<FLAT>(lines, (uint64_t)(i0 + j)) = (uint8_t)(qw[j >> 2] >> (8 * (j & 3)));
         }
     }
     flush_stats(st, s_stats, L.stats);
@@ -520,7 +638,7 @@ cluster_tile_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
 // ------------------------------------------------------------------ long clusters: one block each
 template <bool FLAT>
 __global__ void __launch_bounds__(CL_THREADS)
-cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
+cluster_long_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__restrict__ qs,
                     const uint8_t *__restrict__ lcp, uint32_t n, uint8_t *__restrict__ lines,
                     uint8_t *__restrict__ obase, SmoothLists L)
 {
@@ -543,7 +661,7 @@ cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
     auto lcp_at = [&](int64_t i) -> int { return (i < 0 || i >= nn) ? 0 : (int)lcp[i]; };
     auto F = [&](int64_t i) -> bool {
         if (i <= 0 || i >= nn) return false;
-        return f_flag(lcp_at(i - 1), lcp_at(i), lcp_at(i + 1), false, i == nn - 1);
+        return f_flag(g_sc, lcp_at(i - 1), lcp_at(i), lcp_at(i + 1), false, i == nn - 1);
     };
     const uint32_t count = min(*L.long_count, L.long_cap);
     for (uint32_t ci = blockIdx.x; ci < count; ci += gridDim.x) {
@@ -604,7 +722,7 @@ cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
 #pragma unroll
             for (int k = 0; k < 6; k++) acc.freq[k] = s_freq[k];
             acc.hiq = s_hiq; acc.base_num = s_base; acc.mx = s_mx; acc.isum = (int32_t)s_isum; acc.dsum = s_dsum;
-            Decision d = decide(len, acc, st);
+            Decision d = decide(g_sc, len, acc, st);
             if (d.act == ACT_RULE11) {
                 uint32_t k = atomicAdd(L.r11_count, 1u);
                 if (k < L.r11_cap)
@@ -636,7 +754,7 @@ cluster_long_kernel(const uint8_t *__restrict__ bwt, const uint8_t *__restrict__
 // packed text at SA[row] - 2 (code 0 there = the previous read's terminator = "no preceding base").
 template <bool FLAT>
 __global__ void __launch_bounds__(256)
-rule11_kernel(const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8_t *__restrict__ obase,
+rule11_kernel(SC_ARG, const uint8_t *__restrict__ qs, uint8_t *__restrict__ lines, uint8_t *__restrict__ obase,
               SmoothLists L, const uint8_t *__restrict__ bwt, const void *__restrict__ SA, int sa_wide,
               const uint64_t *__restrict__ T3, const uint32_t *__restrict__ super)
 {
@@ -760,14 +878,15 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     sc.default_q = P->default_q; sc.code_N = (int8_t)A.code_N; sc.acgt_mask = A.acgt_mask;
     sc.nsym = (uint8_t)A.nsym;
     sc.long_len = (uint32_t)std::min<int64_t>(c->opt_long_cluster, 4000);
-    BFQ_CUDA(cudaMemcpyToSymbolAsync(g_sc, &sc, sizeof sc, 0, cudaMemcpyHostToDevice, st));
 #if BFQ_M == 1
-    {
-        static double errtab[256], thr[128];
-        static bool built = false;
-        if (!built) { build_m1_tables(errtab, thr); built = true; }
-        BFQ_CUDA(cudaMemcpyToSymbolAsync(g_errtab, errtab, sizeof errtab, 0, cudaMemcpyHostToDevice, st));
-        BFQ_CUDA(cudaMemcpyToSymbolAsync(g_m1thr, thr, sizeof thr, 0, cudaMemcpyHostToDevice, st));
+    {   // the M=1 tables are the same for every call: written once per device (several contexts may share one)
+        static std::once_flag once[64];
+        std::call_once(once[c->device & 63], [&] {
+            static double errtab[256], thr[128];
+            build_m1_tables(errtab, thr);
+            BFQ_CUDA(cudaMemcpyToSymbol(g_errtab, errtab, sizeof errtab));
+            BFQ_CUDA(cudaMemcpyToSymbol(g_m1thr, thr, sizeof thr));
+        });
     }
 #endif
     uint32_t *d_pile = (uint32_t *)((char *)c->d_small + 2048);
@@ -792,48 +911,57 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     Arena::Mark mk = c->arena.mark();
     if (!flat) {
         ProfScope ps(c, PC_RANK, 2 * n + nlines * 32, 3);
-        rank_count_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, blk);
+        rank_count_kernel<<<nblk, RK_THREADS, 0, st>>>(sc, d_bwt, n, blk);
         rank_scan_kernel<<<1, 1024, 0, st>>>(blk, nblk, d_pile);
-        rank_build_kernel<<<nblk, RK_THREADS, 0, st>>>(d_bwt, n, out->lines);
+        rank_build_kernel<<<nblk, RK_THREADS, 0, st>>>(sc, d_bwt, n, out->lines);
         launch_check(c);
     }
 
     // ---- clusters
     SmoothLists L;
-    L.long_cap = (uint32_t)(n / std::max<uint32_t>(sc.long_len, 1) + 1024);
-    L.r11_cap = (uint32_t)(n / 8 + 1024);
-    L.long_starts = arena_alloc<uint32_t>(c, L.long_cap);
-    L.r11 = arena_alloc<R11Desc>(c, L.r11_cap);
-    unsigned long long *d_stats = arena_alloc<unsigned long long>(c, ST_COUNT + 2);
-    L.stats = d_stats;
-    L.long_count = (uint32_t *)(d_stats + ST_COUNT);
-    L.r11_count = L.long_count + 1;
-    BFQ_CUDA(cudaMemsetAsync(d_stats, 0, (ST_COUNT + 2) * 8, st));
-    {
-        ProfScope ps(c, PC_CLUSTER, 4 * n);
-        if (flat) cluster_tile_kernel<true><<<div_up(n, CL_TILE), CLT_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
-        else cluster_tile_kernel<false><<<div_up(n, CL_TILE), CLT_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
-        launch_check(c);
-    }
-    {
-        ProfScope ps(c, PC_CLUSTER_LONG, 0);
-        if (flat) cluster_long_kernel<true><<<c->num_sms * 2, CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
-        else cluster_long_kernel<false><<<c->num_sms * 2, CL_THREADS, 0, st>>>(d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
-        launch_check(c);
-    }
-    {
-        ProfScope ps(c, PC_RULE11, 0);
-        if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, sa_wide ? 1 : 0, d_t3, nullptr);
-        else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(d_qs, out->lines, out->obase, L, d_bwt, d_sa, 0, d_t3, out->super);
-        launch_check(c);
-    }
-    fetch_small(c, c->h_small, d_stats, (ST_COUNT + 2) * 8);
-    BFQ_CUDA(cudaStreamSynchronize(st));
+    L.long_cap = (uint32_t)(n / std::max<uint32_t>(std::min<uint32_t>(sc.long_len, CL_LONG_MAX), 1) + 1024);
+    L.r11_cap = c->opt_r11_cap > 0 ? (uint32_t)c->opt_r11_cap : (uint32_t)(n / 8 + 1024);
     const uint64_t *h = c->h_small;
     const uint32_t *cnts = (const uint32_t *)(h + ST_COUNT);
+    for (int attempt = 0;; attempt++) {
+        Arena::Mark mk2 = c->arena.mark();
+        L.long_starts = arena_alloc<uint32_t>(c, L.long_cap);
+        L.r11 = arena_alloc<R11Desc>(c, L.r11_cap);
+        unsigned long long *d_stats = arena_alloc<unsigned long long>(c, ST_COUNT + 2);
+        L.stats = d_stats;
+        L.long_count = (uint32_t *)(d_stats + ST_COUNT);
+        L.r11_count = L.long_count + 1;
+        BFQ_CUDA(cudaMemsetAsync(d_stats, 0, (ST_COUNT + 2) * 8, st));
+        {
+            ProfScope ps(c, PC_CLUSTER, 4 * n);
+            if (flat) cluster_tile_kernel<true><<<div_up(n, CL_TILE), CLT_THREADS, 0, st>>>(sc, d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+            else cluster_tile_kernel<false><<<div_up(n, CL_TILE), CLT_THREADS, 0, st>>>(sc, d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+            launch_check(c);
+        }
+        {
+            ProfScope ps(c, PC_CLUSTER_LONG, 0);
+            if (flat) cluster_long_kernel<true><<<c->num_sms * 2, CL_THREADS, 0, st>>>(sc, d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+            else cluster_long_kernel<false><<<c->num_sms * 2, CL_THREADS, 0, st>>>(sc, d_bwt, d_qs, d_lcp, (uint32_t)n, out->lines, out->obase, L);
+            launch_check(c);
+        }
+        {
+            ProfScope ps(c, PC_RULE11, 0);
+            if (flat) rule11_kernel<true><<<c->num_sms * 4, 256, 0, st>>>(sc, d_qs, out->lines, out->obase, L, d_bwt, d_sa, sa_wide ? 1 : 0, d_t3, nullptr);
+            else rule11_kernel<false><<<c->num_sms * 4, 256, 0, st>>>(sc, d_qs, out->lines, out->obase, L, d_bwt, d_sa, 0, d_t3, out->super);
+            launch_check(c);
+        }
+        fetch_small(c, c->h_small, d_stats, (ST_COUNT + 2) * 8);
+        BFQ_CUDA(cudaStreamSynchronize(st));
+        c->arena.release(mk2);
+        if (cnts[0] <= L.long_cap && cnts[1] <= L.r11_cap) break;
+        // A list overflowed (a two-base cluster needs only two rows, so valid input can hold up to n/2 of them): the kernels
+        // counted what they would have stored, and every pass rewrites all rows from the unchanged inputs, so run again with
+        // lists of the counted size.
+        if (attempt) BFQ_FAIL(BFQ_ECAPACITY, "internal cluster list overflow (long %u/%u, two-base %u/%u)", cnts[0], L.long_cap, cnts[1], L.r11_cap);
+        L.long_cap = std::max(L.long_cap, cnts[0]);
+        L.r11_cap = std::max(L.r11_cap, cnts[1]);
+    }
     c->arena.release(mk);
-    if (cnts[0] > L.long_cap || cnts[1] > L.r11_cap)
-        BFQ_FAIL(BFQ_ECAPACITY, "internal cluster list overflow (long %u/%u, two-base %u/%u)", cnts[0], L.long_cap, cnts[1], L.r11_cap);
     if (h[ST_ERR])
         BFQ_FAIL(BFQ_EFREQ3, "a cluster has more than two frequent symbols (the reference asserts, bfq_ext.cpp:683); raise -f");
     if (stats) {
