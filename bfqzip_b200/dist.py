@@ -70,8 +70,11 @@ class GpuEngine:
     def upload(self, reads):
         t = self.torch
         bases, quals, off = reads
-        return (t.from_numpy(np.ascontiguousarray(bases)).to(self.dev), t.from_numpy(np.ascontiguousarray(quals)).to(self.dev),
-                t.from_numpy(np.ascontiguousarray(off, np.uint64).view(np.int64)).to(self.dev))
+        d = (t.from_numpy(np.ascontiguousarray(bases)).to(self.dev), t.from_numpy(np.ascontiguousarray(quals)).to(self.dev),
+             t.from_numpy(np.ascontiguousarray(off, np.uint64).view(np.int64)).to(self.dev))
+        # the engine works on its own stream: the copies (torch's stream) must have landed before it reads them
+        t.cuda.current_stream(self.dev).synchronize()
+        return d
 
     def build(self, rank, world, dreads, nreads, total_bases, params, tb):
         t = self.torch
@@ -176,6 +179,9 @@ def emulate_ranks(engine, reads, params, world: int):
         cnt = rk.numel() - 16
         assert cnt == int(tb[d + 1] - tb[d]), (d, cnt, int(tb[d + 1] - tb[d]))
         lo, hi = rb[d], rb[d + 1]
+        # torch.cat runs on torch's stream, the engine on its own: at 10^8 pairs the engine would otherwise start on a
+        # half-written list (exchange_pairs synchronises the same way after the all-to-all)
+        torch.cuda.current_stream(rk.device).synchronize()
         ob, oq = engine.place(rk, rv, cnt, int(tb[d]), dreads, lo, hi, int(off[hi] - off[lo]))
         obs.append(ob.cpu().numpy()); oqs.append(oq.cpu().numpy())
     return bwt, qs, lcp, np.concatenate(obs), np.concatenate(oqs), stats
