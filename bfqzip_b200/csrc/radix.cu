@@ -11,6 +11,8 @@
 //                       leaves the SM as contiguous, coalesced stores.
 // HBM-bound integer work: no tensor cores.  Algorithmic bytes per pass = 2*(sizeof(K)+4)*n.
 #include "common.cuh"
+#include <algorithm>
+#include <mutex>
 
 namespace bfq {
 
@@ -710,3 +712,106 @@ int radix_sort_pairs32_16(bfq_ctx *c, uint32_t *ka, uint32_t *kb, uint16_t *va, 
 }
 
 } // namespace bfq
+
+// ------------------------------------------------------------------------------ sort without any allocation
+// bfq_sort_pairs_noalloc (include/bfq_gpu.h): the same kernels as radix_sort_pairs64, for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch the passes need -- the
+// per-tile status words of the decoupled look-back, the tile counter and the digit histograms -- lives in ONE file-scope
+// device array of fixed size instead of the context's arena, so every GPU that loads the library holds it until exit
+// and every call shares it: it keeps the last call's contents (what must start at zero is cleared by stream-ordered
+// memsets below), and calls that overlap on the GPU race on it.
+namespace bfq {
+
+constexpr uint64_t NA_MAX_PAIRS = BFQ_NOALLOC_MAX_PAIRS;
+constexpr int NA_ITEMS = 16;
+constexpr uint32_t NA_TILE = RS_THREADS * NA_ITEMS;
+constexpr uint32_t NA_MAX_TILES = (uint32_t)((NA_MAX_PAIRS + NA_TILE - 1) / NA_TILE);
+constexpr size_t NA_STATUS_WORDS = (size_t)NA_MAX_TILES * RS_RADIX;         // u32 status words (n < 2^30)
+constexpr size_t NA_COUNTER_WORDS = 64;                                     // tile counter (one word used; keeps hist aligned)
+constexpr size_t NA_HIST_WORDS = (size_t)RS_MAX_PASSES * RS_RADIX;
+constexpr size_t NA_WORDS = NA_STATUS_WORDS + NA_COUNTER_WORDS + NA_HIST_WORDS;   // 1 MiB + 256 B + 8 KiB
+static_assert(NA_MAX_PAIRS < ((uint64_t)1 << 30), "32-bit status words");
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NA_WORDS];
+
+// In host code the array's name is only a stand-in for the symbol, not a device address: the address is fetched with
+// cudaGetSymbolAddress, once per device and with that device current, and handed to the kernels as an argument.
+constexpr int NA_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mutex;
+static uint32_t *g_noalloc_ptr[NA_MAX_DEVICES] = {nullptr};
+
+static int noalloc_scratch(uint32_t **out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_error("bfq_sort_pairs_noalloc: cudaGetDevice -> %s", cudaGetErrorString(e)); return BFQ_ENODEVICE; }
+    if (dev < 0 || dev >= NA_MAX_DEVICES) { set_error("bfq_sort_pairs_noalloc: device %d out of range", dev); return BFQ_EINVAL; }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[dev]) {
+        uint32_t *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            set_error("bfq_sort_pairs_noalloc: cudaGetSymbolAddress on device %d -> %s", dev, cudaGetErrorString(e));
+            return BFQ_ECUDA;
+        }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return BFQ_OK;
+}
+
+} // namespace bfq
+
+extern "C" int bfq_sort_pairs_noalloc(uint64_t *d_keys_a, uint64_t *d_keys_b, uint32_t *d_vals_a, uint32_t *d_vals_b,
+                                      uint64_t n, int bits, void *cuda_stream, int *result_in_b)
+{
+    using namespace bfq;
+    if (result_in_b) *result_in_b = 0;
+    if (bits < 0 || bits > 64) { set_error("bfq_sort_pairs_noalloc: bits must be 0..64"); return BFQ_EINVAL; }
+    if (n > NA_MAX_PAIRS) {
+        set_error("bfq_sort_pairs_noalloc: %llu pairs exceed the fixed scratch of this entry point (at most %llu); "
+                  "use a context-based call for larger inputs", (unsigned long long)n, (unsigned long long)NA_MAX_PAIRS);
+        return BFQ_ECAPACITY;
+    }
+    if (n == 0 || bits == 0) return BFQ_OK;                 // nothing to order: the input (a) is the result
+    if (!d_keys_a || !d_keys_b || !d_vals_a || !d_vals_b) { set_error("bfq_sort_pairs_noalloc: null pointer"); return BFQ_EINVAL; }
+    uint32_t *scratch = nullptr;
+    const int rc = noalloc_scratch(&scratch);
+    if (rc != BFQ_OK) return rc;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    uint32_t *status = scratch, *tile_counter = scratch + NA_STATUS_WORDS, *hist = tile_counter + NA_COUNTER_WORDS;
+    const RsPasses P = plan_passes(bits);
+    const uint32_t tiles = div_up(n, NA_TILE);
+    cudaError_t e;
+#define NA_CUDA(call)                                                                                        \
+    do {                                                                                                     \
+        e = (call);                                                                                          \
+        if (e != cudaSuccess) { set_error("bfq_sort_pairs_noalloc: %s -> %s", #call, cudaGetErrorString(e)); return BFQ_ECUDA; } \
+    } while (0)
+    // the array keeps the previous call's contents: the histograms are accumulated, so they start at zero
+    NA_CUDA(cudaMemsetAsync(hist, 0, NA_HIST_WORDS * sizeof(uint32_t), st));
+    {
+        const int grid = (int)std::min<uint64_t>((uint64_t)148 * 8, div_up(n, RS_THREADS));   // grid-stride kernel: 8 blocks per B200 SM
+        rs_hist_kernel<uint64_t><<<grid, RS_THREADS, 0, st>>>(d_keys_a, n, P, hist);
+        rs_scan_hist_kernel<<<P.num, RS_RADIX, 0, st>>>(hist);
+        NA_CUDA(cudaGetLastError());
+    }
+    uint64_t *kin = d_keys_a, *kout = d_keys_b;
+    uint32_t *vin = d_vals_a, *vout = d_vals_b;
+    const size_t dyn = (size_t)NA_TILE * sizeof(uint64_t);   // 32 KiB: below the opt-in threshold, no attribute call needed
+    for (int p = 0; p < P.num; p++) {
+        // status words (flag 0 = "not published yet") and the tile counter of THIS pass: the words of the used tiles and
+        // the counter are contiguous only when all tiles are used, so they are cleared separately
+        NA_CUDA(cudaMemsetAsync(status, 0, (size_t)tiles * RS_RADIX * sizeof(uint32_t), st));
+        NA_CUDA(cudaMemsetAsync(tile_counter, 0, NA_COUNTER_WORDS * sizeof(uint32_t), st));
+        rs_onesweep_kernel<uint64_t, uint32_t, uint32_t, NA_ITEMS><<<tiles, RS_THREADS, dyn, st>>>(
+            kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX, status, tile_counter);
+        NA_CUDA(cudaGetLastError());
+        std::swap(kin, kout);
+        std::swap(vin, vout);
+    }
+#undef NA_CUDA
+    if (result_in_b) *result_in_b = P.num & 1;
+    return BFQ_OK;
+}

@@ -251,3 +251,18 @@ class BfqGpu:
         sa = np.empty(n, np.uint32)
         self._chk(self.lib.bfq_debug_suffix_array(self.h, _ptr(bases), _ptr(off), C.c_uint64(nreads), _ptr(sa)))
         return sa
+
+
+NOALLOC_MAX_PAIRS = 1 << 22          # BFQ_NOALLOC_MAX_PAIRS (include/bfq_gpu.h)
+
+
+def sort_pairs_noalloc(d_keys_a, d_keys_b, d_vals_a, d_vals_b, n: int, bits: int, cuda_stream: int = 0, M: int = 2, B: int = 0) -> int:
+    """bfq_sort_pairs_noalloc: context-free, allocation-free radix sort of device-resident (u64, u32) pairs on the
+    current device; asynchronous on ``cuda_stream``.  Returns 0 when the result is in the (a) buffers, 1 for (b)."""
+    lib = load(M, B)
+    flag = C.c_int(0)
+    rc = lib.bfq_sort_pairs_noalloc(_ptr(d_keys_a), _ptr(d_keys_b), _ptr(d_vals_a), _ptr(d_vals_b), C.c_uint64(n),
+                                    C.c_int(bits), C.c_void_p(cuda_stream or 0), C.byref(flag))
+    if rc != 0:
+        raise BfqError(rc, lib.bfq_last_error().decode())
+    return int(flag.value)

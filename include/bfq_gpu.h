@@ -192,6 +192,23 @@ void bfq_prof_reset(bfq_ctx *ctx);
 /* number of kernel launches issued by this ctx since creation (bench.py's gpu_launches) */
 uint64_t bfq_launch_count(bfq_ctx *ctx);
 
+/* ---- allocation-free entry point ------------------------------------------------------- */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Stable LSD radix sort of (u64 key, u32 value) pairs on the low `bits` key bits -- the onesweep kernels of
+ * bfq_debug_sort_pairs -- on DEVICE buffers of the CURRENT device, enqueued on `cuda_stream` (NULL = default
+ * stream).  It needs no context, allocates nothing (no cudaMalloc / cudaFree / allocating library call) and does
+ * not synchronise: the result is valid once the work enqueued on the stream has finished.
+ *   d_keys_a / d_vals_a  input (overwritten); d_keys_b / d_vals_b  second ping-pong buffer, n entries each;
+ *   *result_in_b = 0: the sorted pairs are in (a), 1: in (b)   (= number of 8-bit passes, ceil(bits/8), modulo 2).
+ * LIMIT: n <= BFQ_NOALLOC_MAX_PAIRS.  The scratch of the passes (per-tile status words, tile counter, digit
+ * histograms: 1 MiB + 8.25 KiB) is a fixed device array inside the library, held by every GPU that loads it until the
+ * process exits.  Larger n -> BFQ_ECAPACITY (use the context-based calls).  ALL calls on a device share that array:
+ * calls that overlap on the GPU (different streams, or several host threads) race on it -- serialise them. */
+#define BFQ_NOALLOC_MAX_PAIRS (1u << 22)
+int bfq_sort_pairs_noalloc(uint64_t *d_keys_a, uint64_t *d_keys_b, uint32_t *d_vals_a, uint32_t *d_vals_b,
+                           uint64_t n, int bits, void *cuda_stream, int *result_in_b);
+
 /* ---- test hooks (exercise one kernel family through the same ABI) ---------------------- */
 /* Stable LSD radix sort of (key, value) pairs on the low `bits` bits; host buffers, in place. */
 int bfq_debug_sort_pairs(bfq_ctx *ctx, uint64_t *keys, uint32_t *vals, uint64_t n, int bits);
