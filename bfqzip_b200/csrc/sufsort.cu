@@ -895,7 +895,9 @@ static void launch_group_tile(bfq_ctx *c, const K *keys, const GroupTileArgsT<P>
         B.tile0 = s * per;
         const uint32_t cnt = std::min(per, ntiles - B.tile0);
         {
-            ProfScope ps(c, PC_GROUP, (uint64_t)cnt * GT_T * (sizeof(K) + 4 + 3 + 4 * (uint64_t)A.W));
+            // DRAM bytes per row: key + position in, the three file bytes out, the suffix array when it is kept.  The packed text
+            // the members are compared through is served by L2 (pinned) and is NOT counted: this kernel is issue-bound.
+            ProfScope ps(c, PC_GROUP, (uint64_t)cnt * GT_T * (sizeof(K) + sizeof(P) + 3 + (A.SA ? sizeof(P) : 0)));
             group_tile_kernel<K, P><<<cnt, GT_THREADS, smem, c->stream>>>(keys, B);
             BFQ_CUDA(cudaGetLastError());
         }

@@ -118,10 +118,14 @@ def exchange_pairs(keys, vals, counts: np.ndarray, group=None):
     return rkeys, rvals, sum(rc)
 
 
-def run_single_collection(engine, reads, params, rank: int, world: int, group=None, dreads=None):
-    """One rank's share.  Returns (slice dict, (out_bases, out_quals) of reads [read_lo, read_hi), (read_lo, read_hi), stats)."""
+def run_single_collection(engine, reads, params, rank: int, world: int, group=None, dreads=None, timing: dict | None = None):
+    """One rank's share.  Returns (slice dict, (out_bases, out_quals) of reads [read_lo, read_hi), (read_lo, read_hi), stats).
+    timing (optional): filled with this rank's seconds per stage -- build (range selection, sort, group ordering, smoothing,
+    pair emission: bfq_dist_build, which returns synchronised), exchange (the all-to-all), place (bfq_dist_place)."""
+    import time
     import torch
     import torch.distributed as dist
+    t0 = time.perf_counter()
     off = np.ascontiguousarray(reads[2], np.uint64)
     nreads = len(off) - 1
     total = int(off[-1])
@@ -130,16 +134,22 @@ def run_single_collection(engine, reads, params, rank: int, world: int, group=No
     if dreads is None:
         dreads = engine.upload(reads)
     sl = engine.build(rank, world, dreads, nreads, total, params, tb)
+    t1 = time.perf_counter()
     if world > 1:
         rkeys, rvals, cnt = exchange_pairs(sl["keys"], sl["vals"], sl["counts"], group)
     else:
         rkeys, rvals, cnt = sl["keys"], sl["vals"], int(sl["counts"][0])
+    t2 = time.perf_counter()
     lo, hi = rb[rank], rb[rank + 1]
     expect = int(tb[rank + 1] - tb[rank])
     if cnt != expect:
         raise RuntimeError(f"rank {rank}: received {cnt} rows for {expect} text positions")
     nb = int(off[hi] - off[lo])
     ob, oq = engine.place(rkeys, rvals, cnt, int(tb[rank]), dreads, lo, hi, nb)
+    if timing is not None:
+        t3 = time.perf_counter()
+        for k, v in (("build", t1 - t0), ("exchange", t2 - t1), ("place", t3 - t2)):
+            timing[k] = timing.get(k, 0.0) + v
     stats = dict(sl["stats"])
     if world > 1:
         v = torch.tensor([stats[k] for k in STAT_SUM_KEYS], dtype=torch.int64, device=rkeys.device)

@@ -49,3 +49,14 @@ def format_fastq(bases: np.ndarray, quals: np.ndarray, off: np.ndarray, headers=
 def write_fastq(path: str, bases, quals, off, headers=None) -> None:
     with open(path, "wb") as f:
         f.write(format_fastq(bases, quals, off, headers))
+
+
+def format_fastq_fixed(bases: np.ndarray, quals: np.ndarray, nreads: int, read_len: int) -> bytes:
+    """format_fastq for a fixed-length collection with '@' headers, as one numpy reshape (millions of reads per second)."""
+    rec = np.empty((nreads, 2 * read_len + 6), np.uint8)
+    rec[:, 0] = ord("@"); rec[:, 1] = 10
+    rec[:, 2:2 + read_len] = np.asarray(bases, np.uint8).reshape(nreads, read_len)
+    rec[:, 2 + read_len] = 10; rec[:, 3 + read_len] = ord("+"); rec[:, 4 + read_len] = 10
+    rec[:, 5 + read_len:5 + 2 * read_len] = np.asarray(quals, np.uint8).reshape(nreads, read_len)
+    rec[:, 5 + 2 * read_len] = 10
+    return rec.tobytes()

@@ -133,3 +133,28 @@ def test_gpu_blocks_equal_oracle_blocks():
     for m in (0, 1):
         assert all(np.array_equal(a, b) for a, b in zip(got[m], exp[m]))
     g.close()
+
+
+def test_counter_based_generator_blocks_equal_the_split_of_the_whole_collection():
+    """bench.py generates every config-4 block on the GPU that processes it (synth.hash_paired_block_torch): the block must
+    be exactly what parallel.make_blocks cuts out of the whole paired collection (split_fastq / split_fastq_2 semantics),
+    and the torch version must give the bytes of the numpy version."""
+    import torch
+    npairs, L, seed, frag, nb = 4100, 40, 1003, 90, 8
+    r1, r2 = synth.hash_paired(npairs, L, seed, coverage=40.0, fragment=frag)
+    g = synth.hash_genome_len(2 * npairs, L, 40.0, frag)
+    blocks = parallel.make_blocks(r1, nb, r2)
+    cuts = parallel.split_blocks(npairs, nb)
+    assert len(blocks) == len(cuts) == nb
+    for (reads, n1), (lo, hi) in zip(blocks, cuts):
+        b, q, off = synth.hash_paired_block_torch(torch, torch.device("cpu"), npairs, L, seed, g, frag, lo, hi)
+        assert n1 == hi - lo
+        assert np.array_equal(reads[0], b.numpy()) and np.array_equal(reads[1], q.numpy()) and np.array_equal(reads[2], off)
+    # the model: every read comes from the genome (mate 2 reverse-complemented), ~1 % errors, N at offset 7 of every 1000th read
+    assert set(np.unique(r1[0]).tolist()) == set(b"ACGNT") and r1[0][7] == ord("N") and r1[1][7] == ord("#")
+    low = (r1[1] < 33 + 20).mean()
+    assert 0.005 < low < 0.02
+    # chunking on the device does not change the result
+    a = synth.hash_reads_torch(torch, torch.device("cpu"), 1000, 30, 5, 2000, chunk_reads=64)
+    h = synth.hash_reads(1000, 30, 5, 2000)
+    assert np.array_equal(a[0].numpy(), h[0]) and np.array_equal(a[1].numpy(), h[1])
