@@ -251,7 +251,8 @@ def reference_arm(args):
                       f"{parts[0][0]:.1f} s (1 thread, inherent) + bfq_ext -T {cores} {parts[0][1]:.1f} s; unmodified reference binaries (oracle/_ref)")
             # the other two legs SURVEY 8(d) lists: what the driver really runs (eGap + 1 thread) on a stated sample -- eGap alone
             # needs ~10 minutes for the full collection -- and the whole collection as eight concurrent block pipelines
-            n_eg = 40_000 // (quick or 1)
+            # BFQ_BENCH_EGAP_FULL=1: the whole collection through eGap too (minutes; run once per pool, recorded in profiles/)
+            n_eg = (W["nreads"] if os.environ.get("BFQ_BENCH_EGAP_FULL") else 40_000) // (quick or 1)
             te, pe = ref_cfg2(n_eg, 1, step1="egap")
             variants["egap_bfq_ext_T1"] = {"value": n_eg * W["read_len"] / te / 1e9, "unit": "Gbases/s", "cores": 1,
                                            "sample": f"first {n_eg} reads of config 2 ({100.0 * n_eg / W['nreads']:.0f} %): eGap --em {pe[0][0]:.1f} s + bfq_ext -T 1 {pe[0][1]:.1f} s (BFQzip_ext.py:173-177, 207-215)"}

@@ -129,3 +129,75 @@ def test_bfq_ext_component_streams_and_host_paths(tmp_path):
     assert open(out + ".fq", "rb").read() == outs["dev"][3]
     assert open(out + ".fq.dna", "rb").read() == b"".join(x + b"\n" for x in lines[1::4])
     assert open(out + ".fq.qs", "rb").read() == b"".join(x + b"\n" for x in lines[3::4])
+
+
+DRIVER = os.path.join(H.REF_DIR, "driver")
+
+
+def _driver_tree(tmp_path):
+    """The tree INTEGRATION.md section A describes: the reference's UNMODIFIED BFQzip_ext.py + checkFASTQ.py (copied into
+    git-ignored oracle/_ref/driver/ by oracle/Makefile) with the two drop-in tools where the driver looks for its own
+    (it resolves them relative to its directory, BFQzip_ext.py:55,173,207)."""
+    d = tmp_path / "bfqzip"
+    (d / "external" / "egap").mkdir(parents=True)
+    (d / "src_ext_mem").mkdir()
+    for f in ("BFQzip_ext.py", "checkFASTQ.py"):
+        (d / f).write_bytes(open(os.path.join(DRIVER, f), "rb").read())
+    os.symlink(os.path.join(BIN, "eGap"), d / "external" / "egap" / "eGap")
+    os.symlink(os.path.join(BIN, "bfq_ext"), d / "src_ext_mem" / "bfq_ext")
+    # Step 5 (BFQzip_ext.py:248-272) hands the streams to the host entropy coders `7z a -mm=PPMd` and external/libbsc/bsc
+    # (resolved relative to the cwd).  Both are out of scope (SURVEY section 8) and neither exists on the GPU box; a missing 7z
+    # would end the driver with an uncaught FileNotFoundError before its final report.  Stand-ins that COPY their input let
+    # the unmodified driver run to its end; nothing of steps 1-4 depends on them.
+    stub = tmp_path / "stubs"
+    (stub).mkdir()
+    (stub / "7z").write_text("#!/bin/sh\n# 7z a -mm=PPMd OUT IN\ncp \"$4\" \"$3\"\n")
+    (d / "external" / "libbsc").mkdir()
+    (d / "external" / "libbsc" / "bsc").write_text("#!/bin/sh\n# bsc e IN OUT -T\ncp \"$2\" \"$3\"\n")
+    os.chmod(stub / "7z", 0o755); os.chmod(d / "external" / "libbsc" / "bsc", 0o755)
+    return d, stub
+
+
+@pytest.mark.gpu
+def test_unmodified_reference_driver_runs_end_to_end(tmp_path):
+    """BASELINE config 1 as it is DEFINED: `python3 BFQzip_ext.py reads.fastq -o out --m3` with the reference's own driver
+    (BFQzip_ext.py:165-244, 310-318): step 1 (our eGap, --mem 0 on this 24 KB input), step 2 (headers), step 3 (our
+    bfq_ext with -H), step 4 (component streams), step 5 (stand-ins), final report; then checkFASTQ.py:18-32 on out.fq."""
+    if not os.path.exists(os.path.join(DRIVER, "BFQzip_ext.py")):
+        pytest.skip("oracle/_ref/driver is not built (make -C oracle ref, needs /root/reference)")
+    _need_tools()
+    import sys
+    g, headers, _ = _example(tmp_path)
+    d, stub = _driver_tree(tmp_path)
+    fq = d / "reads.fastq"
+    fastq.write_fastq(str(fq), g["bases"], g["quals"], g["off"], headers)
+    env = dict(os.environ, PATH=str(stub) + os.pathsep + os.environ.get("PATH", ""))
+    r = subprocess.run([sys.executable, "BFQzip_ext.py", "reads.fastq", "-o", "out", "--m3"], cwd=d, env=env, capture_output=True)
+    log = (d / "out.log").read_text(errors="replace") if (d / "out.log").exists() else ""
+    assert r.returncode == 0, (r.stdout.decode(errors="replace")[-2000:], r.stderr.decode(errors="replace")[-2000:], log[-2000:])
+    stdout = r.stdout.decode()
+    assert "Valid FASTQ file!" in stdout and "=== results ===" in stdout
+    assert "--mem 0 " in stdout                                        # SURVEY F4: the driver asks eGap for 0 MB on small files
+    # step 1: the three files, byte-identical to the reference's (EOS byte 0 in the eGap spelling)
+    bwt = g["bwt"].copy(); bwt[g["bwt"] == 35] = 0
+    qs = g["qs"].copy(); qs[g["bwt"] == 35] = 0
+    assert np.array_equal(np.fromfile(d / "out.bwt", np.uint8), bwt)
+    assert np.array_equal(np.fromfile(d / "out.bwt.qs", np.uint8), qs)
+    assert np.array_equal(np.fromfile(d / "out.1.lcp", np.uint8), g["lcp"])
+    # step 3: the .fq of the reference, its statistics block in the log
+    assert hashlib.md5((d / "out.fq").read_bytes()).hexdigest() == "9178301c8ef6c9864d5ebfccf47313d4"
+    st = H.parse_ref_stats(log)
+    assert (st["clusters"], st["qs_smoothed"], st["modified"]) == (387, 4198, 10)
+    # steps 2 and 4 ran on their inputs; step 5's stand-ins produced what the final report sizes up
+    assert (d / "out.h").read_bytes() == b"".join(h + b"\n" for h in headers)
+    for f in ("out.fq.dna", "out.fq.qs", "out.h.7z", "out.fq.dna.7z", "out.fq.qs.7z", "out.fq.qs.bsc"):
+        assert (d / f).exists(), f
+    # the reference's own validity check on the result
+    sys.path.insert(0, str(d))
+    try:
+        import importlib
+        checker = importlib.import_module("checkFASTQ")
+        assert checker.checkFASTQ(str(d / "out.fq")) is True
+    finally:
+        sys.path.remove(str(d))
+        sys.modules.pop("checkFASTQ", None)
