@@ -98,6 +98,12 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     const uint64_t N = total_bases + nreads;
     if (stats) memset(stats, 0, sizeof *stats);
     if (N == 0) return;
+    // The fused calls return the reads under the CALLER's offsets.  The reference truncates a read longer than -l to its
+    // last -l symbols (decode.cpp:605), which changes every later offset: that case is served by bfq_build_ebwt +
+    // bfq_smooth_rebuild (which returns the new offsets); here it is refused instead of returning shifted reads.
+    if (mx > (uint64_t)P->max_len)
+        BFQ_FAIL(BFQ_EINVAL, "a read has %llu symbols but max_len (-l) is %d: the fused pipeline keeps the caller's offsets and cannot truncate; "
+                 "raise max_len (<= 255) or use bfq_build_ebwt + bfq_smooth_rebuild", (unsigned long long)mx, P->max_len);
     if (!d_bwt) d_bwt = arena_alloc<uint8_t>(c, N + 64);
     if (!d_qs) d_qs = arena_alloc<uint8_t>(c, N + 64);
     if (!d_lcp) d_lcp = arena_alloc<uint8_t>(c, N + 64);
@@ -106,7 +112,7 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     // auto: from flat_min_rows rows on; a device-resident call (no host sink: nothing leaves while the walk runs, so the walk's
     // overlap with the copies does not count) already from flat_min_rows_dev on, where the walk lines outgrow L2
     const uint64_t auto_min = (uint64_t)(c->sink ? c->opt_flat_min_rows : std::min(c->opt_flat_min_rows, c->opt_flat_min_rows_dev));
-    const bool flat = mx <= (uint64_t)P->max_len && (c->opt_rebuild == 1 || (c->opt_rebuild == 0 && N >= auto_min));
+    const bool flat = c->opt_rebuild == 1 || (c->opt_rebuild == 0 && N >= auto_min);
     uint32_t *d_sa = flat ? arena_alloc<uint32_t>(c, N + 16) : nullptr;
     uint64_t *d_t3 = flat ? arena_alloc<uint64_t>(c, packed_text_words(N)) : nullptr;
     {
@@ -131,15 +137,8 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
     smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats, d_sa, d_t3);
     c->trace("part B done", c->stream);
     if (S.nreads != nreads) BFQ_FAIL(BFQ_ECUDA, "internal error: %llu end-markers for %llu reads", (unsigned long long)S.nreads, (unsigned long long)nreads);
-    if (flat) {
-        unpermute_dev(c, S, d_bwt, d_sa, d_off, nreads, d_out_bases, d_out_quals);
-    } else if (mx <= (uint64_t)P->max_len) {
-        rebuild_dev(c, S, P, d_off, d_out_bases, d_out_quals, nullptr, nullptr);
-    } else {
-        // reads longer than -l are truncated by the reference (decode.cpp:605): general path
-        uint64_t *d_oo = arena_alloc<uint64_t>(c, nreads + 1);
-        rebuild_dev(c, S, P, nullptr, d_out_bases, d_out_quals, d_oo, nullptr);
-    }
+    if (flat) unpermute_dev(c, S, d_bwt, d_sa, d_off, nreads, d_out_bases, d_out_quals);
+    else rebuild_dev(c, S, P, d_off, d_out_bases, d_out_quals, nullptr, nullptr);
     c->trace("part C done", c->stream);
     if (c->sink && c->sink->out_copied) { BFQ_CUDA(cudaEventRecord(c->ev_copy, c->copy_stream)); c->trace("reads on host (copy stream)", c->copy_stream); }
     if (h_bwt || h_qs || h_lcp || (c->sink && c->sink->out_copied))

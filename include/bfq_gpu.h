@@ -113,7 +113,10 @@ int bfq_smooth_rebuild(bfq_ctx *ctx, const uint8_t *bwt, const uint8_t *qs, cons
                        uint64_t off_capacity, bfq_stats *stats);
 
 /* Parts A+B+C fused.  bwt/qs/lcp may be NULL (then they are not copied back).
- * out_bases/out_quals: off[nreads] bytes (read lengths are unchanged; offsets == off). */
+ * out_bases/out_quals: off[nreads] bytes (read lengths are unchanged; offsets == off).
+ * A read longer than params->max_len is refused with BFQ_EINVAL by every fused call (bfq_pipeline, bfq_pipeline_dev,
+ * bfq_pipeline_fastq): the reference truncates such a read (decode.cpp:605), which would move every later offset;
+ * bfq_build_ebwt + bfq_smooth_rebuild serve that case and return the new offsets. */
 int bfq_pipeline(bfq_ctx *ctx, const uint8_t *bases, const uint8_t *quals, const uint64_t *off,
                  uint64_t nreads, const bfq_params *params,
                  uint8_t *bwt, uint8_t *qs, uint8_t *lcp,

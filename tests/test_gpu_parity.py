@@ -342,3 +342,37 @@ def test_pipeline_roundtrip_1M():
             g.set_option("host_slices", 16)
         assert st3 == st and np.array_equal(b2, bwt) and np.array_equal(q2, qs) and np.array_equal(l2, lcp)
         assert np.array_equal(ob2, ob) and np.array_equal(oq2, oq)
+
+
+def test_fused_calls_refuse_reads_longer_than_max_len():
+    """A read longer than -l is truncated by the reference (decode.cpp:605), which moves every later offset.  The fused
+    calls return the reads under the CALLER's offsets, so they refuse such input (BFQ_EINVAL) instead of returning shifted
+    reads; the two-call path truncates like the reference and returns the new offsets."""
+    import torch
+    bases, quals, off = synth.make_reads(300, 60, 4242, var_len=True)
+    P = lib.default_params(eos=35, max_len=40)
+    assert int(np.diff(off.astype(np.int64)).max()) > 40
+    c = ctx(2, 0)
+    with pytest.raises(lib.BfqError) as ei:
+        c.pipeline(bases, quals, off, P)
+    assert ei.value.code == -3 and "max_len" in str(ei.value)
+    dev = torch.device("cuda", 0)
+    d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    n = len(bases) + len(off) - 1
+    e = lambda k: torch.empty(k + 64, dtype=torch.uint8, device=dev)
+    with pytest.raises(lib.BfqError) as ei:
+        c.pipeline_dev(d(bases), d(quals), d(off.view(np.int64)), len(off) - 1, len(bases), P, e(n), e(n), e(n), e(n), e(n))
+    assert ei.value.code == -3
+    from bfqzip_b200 import fastq
+    with pytest.raises(lib.BfqError) as ei:
+        c.pipeline_fastq(fastq.format_fastq(bases, quals, off), P)
+    assert ei.value.code == -3
+    # the two-call path: truncated reads, new offsets, equal to the oracle's reconstruction with the same -l
+    bwt, qs, lcp = c.build_ebwt(bases, quals, off, 35)
+    ob, oq, o2, st = c.smooth_rebuild(bwt, qs, lcp, P)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(bwt, qs, lcp, H.make_params(M=2, B=0, max_len=40))
+    assert np.array_equal(o2, eoff) and np.array_equal(ob, eb) and np.array_equal(oq, eq)
+    assert int(np.diff(o2.astype(np.int64)).max()) == 40
+    # and the context is usable afterwards
+    (b2, q2, l2), _, _ = c.pipeline(bases, quals, off, lib.default_params(eos=35, max_len=250))
+    assert np.array_equal(b2, bwt)
