@@ -34,6 +34,7 @@ struct SmoothConst {
     uint8_t code2byte[8];
     int32_t K, m, qthr;
     float fthr;
+    int32_t fT;          // ceil(fthr): (uchar)(100 * f / n) >= fthr  <=>  100 * f >= fT * n  (the left side is an integer)
     uint8_t default_q;
     int8_t code_N;
     uint8_t acgt_mask;
@@ -263,8 +264,9 @@ __device__ __forceinline__ Decision decide(const SmoothConst &g_sc, uint32_t len
 #pragma unroll
     for (uint32_t c = 1; c <= 5; c++) {
         if (a.freq[c] > 0) {
-            uint8_t perc = (uint8_t)((100ull * a.freq[c]) / a.base_num);
-            if ((float)perc >= g_sc.fthr) { if (nF < 3) F[nF] = c; nF++; }
+            // bfq_ext.cpp:665-677: perc = (uchar)((100 * freq) / base_num), frequent when perc >= fthr.  perc is an integer
+            // in 0..100, so perc >= fthr <=> perc >= ceil(fthr) <=> 100 * freq >= ceil(fthr) * base_num: no division
+            if (100ll * (long long)a.freq[c] >= (long long)g_sc.fT * (long long)a.base_num) { if (nF < 3) F[nF] = c; nF++; }
         }
     }
     if (nF >= 3) { st[ST_ERR]++; return d; }
@@ -368,6 +370,22 @@ __device__ __forceinline__ void flush_stats(const uint32_t *st, uint32_t *s_stat
 
 // bit 0 of each of the four bytes of x -> bits 0..3
 __device__ __forceinline__ uint32_t gather_bit0(uint32_t x) { return ((x & 0x01010101u) * 0x01020408u) >> 24; }
+// ---- four rows per instruction: packed-byte helpers (flags live in bit 7 of every byte)
+// a >= b per unsigned byte
+__device__ __forceinline__ uint32_t ge4(uint32_t a, uint32_t b)
+{
+    const uint32_t t = (a | 0x80808080u) - (b & 0x7F7F7F7Fu);         // bit 7: low 7 bits of a >= low 7 bits of b (no borrow crosses a byte)
+    return ((a & ~b) | (~(a ^ b) & t)) & 0x80808080u;
+}
+// bit 7 of each of the four bytes -> bits 0..3
+__device__ __forceinline__ uint32_t gather_bit7(uint32_t x) { return (((x >> 7) & 0x01010101u) * 0x01020408u) >> 24; }
+// bits 0..3 -> 0xFF in the bytes whose bit is set
+__device__ __forceinline__ uint32_t expand4(uint32_t m4) { return (((m4 & 15u) * 0x00204081u) & 0x01010101u) * 0xFFu; }
+// rows (bits) whose 3-bit code, given as bit planes, equals c
+__device__ __forceinline__ uint32_t code_rows(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t c)
+{
+    return ((c & 1u) ? p0 : ~p0) & ((c & 2u) ? p1 : ~p1) & ((c & 4u) ? p2 : ~p2);
+}
 
 template <bool FLAT>
 __global__ void __launch_bounds__(CLT_THREADS, 4)
@@ -420,7 +438,20 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
     }
     const uint32_t valid = full ? 0xFFFFu : (i0 < nn ? (1u << (nn - i0)) - 1u : 0u);          // rows of the chunk inside the BWT
     uint32_t f16 = 0;
-    {
+    if (vec && i0 > 0 && i0 + 17 <= nn && g_sc.K >= 1 && g_sc.K <= 255) {
+        // interior chunk (no row is the first or the last of the BWT): the 3-point stencil on four rows at a time.
+        // f = (l0 >= K) && !(lm > l0 && l0 <= lp)  =  (l0 >= K) && (l0 >= lm || !(lp >= l0))
+        const uint32_t K4 = (uint32_t)g_sc.K * 0x01010101u;
+        const uint32_t prevw = (uint32_t)lcp[i0 - 1] << 24, nextw = lcp[i0 + 16];
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+            const uint32_t l0 = wl[w];
+            const uint32_t lm = __funnelshift_l(w ? wl[w - 1] : prevw, l0, 8);          // the LCP of the row before, per byte
+            const uint32_t lp = __funnelshift_r(l0, w < 3 ? wl[w + 1] : nextw, 8);       // ... of the row after
+            const uint32_t f = ge4(l0, K4) & (ge4(l0, lm) | ~ge4(lp, l0));
+            f16 |= gather_bit7(f) << (4 * w);
+        }
+    } else {
         const uint32_t lprev = (i0 > 0 && i0 - 1 < nn) ? lcp[i0 - 1] : 0u, lnext = (i0 + 16 < nn) ? lcp[i0 + 16] : 0u;
 #pragma unroll
         for (int j = 0; j < 16; j++) {
@@ -517,36 +548,30 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
                     atomicAdd(acc + 1, __popc(m3) | (__popc(m4) << 10) | (__popc(m5) << 20));
                     atomicAdd(acc + 2, __popc(m1 & hq) | (__popc(m2 & hq) << 10) | (__popc(m3 & hq) << 20));
                     atomicAdd(acc + 3, __popc(m4 & hq) | (__popc(m5 & hq) << 10));
-                }
-            }
-        }
 #if BFQ_M == 0 || BFQ_M == 3
-        {   // largest quality (M=0) / sum of the qualities (M=3) of the non-EOS rows, per cluster
-            uint32_t cur = ord0 - 1u - base, X = 0;
+                    // largest quality (M=0) / sum of the qualities (M=3) of the segment's non-EOS rows, four rows at a time
+                    const uint32_t rows = seg & ~m0;
+                    uint32_t X = 0;
 #pragma unroll
-            for (int j = 0; j < 16; j++) {
-                cur += (startm >> j) & 1u;
-                const uint32_t c = (cw[j >> 2] >> (8 * (j & 3))) & 255u, q = (qw[j >> 2] >> (8 * (j & 3))) & 255u;
-                if (((inm >> j) & 1u) && c) {
+                    for (int w = 0; w < 4; w++) {
+                        const uint32_t qm = qw[w] & expand4(rows >> (4 * w));
 #if BFQ_M == 0
-                    X = max(X, q);
+                        X = __vmaxu4(X, qm);
 #else
-                    X += q;
-#endif
-                }
-                if (((endm >> j) & 1u) || j == 15) {
-                    if (X && cur < cnt && !((leadm >> j) & 1u)) {
-#if BFQ_M == 0
-                        atomicMax(s_acc + cur * CL_ACCW + 4, X);
-#else
-                        atomicAdd(s_acc + cur * CL_ACCW + 4, X);
+                        X = __dp4a(qm, 0x01010101u, X);
 #endif
                     }
-                    X = 0;
+#if BFQ_M == 0
+                    X = __vmaxu4(X, X >> 16);
+                    X = max(X & 255u, (X >> 8) & 255u);
+                    if (X) atomicMax(acc + 4, X);
+#else
+                    if (X) atomicAdd(acc + 4, X);
+#endif
+#endif
                 }
             }
         }
-#endif
         __syncthreads();
         // ---- 4. one thread per cluster: rules 7-9
         for (uint32_t k = tid; k < cnt; k += CLT_THREADS) {
@@ -588,24 +613,54 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
             s_dec[k] = dec;
         }
         __syncthreads();
-        // ---- 5. rule 10, row by row in registers
+        // ---- 5. rule 10 (bfq_ext.cpp:546-573) on the thread's 16 rows in registers.  Per segment (= the rows of one cluster
+        // inside this chunk) the decision gives three row sets as bit masks: rows whose base is replaced (bit 7 of the stored
+        // quality), rows that take the new quality, rows that take min(quality, new quality).  They are applied to the packed
+        // qualities four rows at a time; only the (rare) replaced bases are written row by row.
         if (inm & ~leadm) {
-            uint32_t cur = ord0 - 1u - base, dec = 0;
-            if (cur < cnt) dec = s_dec[cur];
+            const uint32_t nz = p0 | p1 | p2;
+            uint32_t MOD = 0, EQ = 0, MINC = 0;                  // rows of the chunk, over all its segments
+            uint32_t nq[4] = {0, 0, 0, 0};                       // the new quality of the row's cluster, per byte
+            uint32_t m = inm & ~leadm;
+            while (m) {
+                const int a = __ffs(m) - 1;
+                const uint32_t em = endm >> a;
+                const int slen = em ? __ffs(em) : 16 - a;
+                const uint32_t seg = ((1u << slen) - 1u) << a;
+                m &= ~seg;
+                const uint32_t o = ord0 + __popc(startm & ((2u << a) - 1u)) - 1u - base;
+                const uint32_t dec = o < cnt ? s_dec[o] : 0u;
+                if (r0 >= CL_TILE && (dec & 2u)) extm |= seg;   // rows past the tile of a cluster this block closed
+                if (dec & 1u) {
+                    const uint32_t sym = (dec >> 4) & 15u, hiq = (dec >> 8) & 255u;
+                    const uint32_t eq = code_rows(p0, p1, p2, sym) & seg;
+                    uint32_t hi = 0;                             // rows whose symbol has a high-quality occurrence in the cluster
 #pragma unroll
-            for (int j = 0; j < 16; j++) {
-                if ((startm >> j) & 1u) { cur++; dec = cur < cnt ? s_dec[cur] : 0u; }
-                if (((inm & ~leadm) >> j) & 1u) {
-                    if (r0 + j >= CL_TILE && (dec & 2u)) extm |= 1u << j;
-                    if (dec & 1u) {
-                        const uint32_t c = (cw[j >> 2] >> (8 * (j & 3))) & 255u;
-                        const uint8_t q = (uint8_t)(qw[j >> 2] >> (8 * (j & 3)));
-                        const uint8_t o = rule10_row(c, q, (dec >> 4) & 15u, (dec >> 8) & 255u, (uint8_t)(dec >> 16), st);
-                        if (o != q) {
-                            qw[j >> 2] = (qw[j >> 2] & ~(255u << (8 * (j & 3)))) | ((uint32_t)o << (8 * (j & 3)));
-                            if (o & 0x80) obase[i0 + j] = g_sc.code2byte[(dec >> 4) & 15u];
-                        }
+                    for (uint32_t c = 1; c <= 5; c++) if ((hiq >> c) & 1u) hi |= code_rows(p0, p1, p2, c);
+                    const uint32_t other = nz & seg & ~eq;
+                    const uint32_t mod = other & ~hi;
+                    MOD |= mod; EQ |= eq; MINC |= other & hi;
+                    const uint32_t nq4 = ((dec >> 16) & 255u) * 0x01010101u;
+#pragma unroll
+                    for (int w = 0; w < 4; w++) nq[w] |= nq4 & expand4(seg >> (4 * w));
+                    if (mod) {
+                        const uint8_t symb = g_sc.code2byte[sym];
+                        uint32_t mm = mod;
+                        while (mm) { obase[i0 + __ffs(mm) - 1] = symb; mm &= mm - 1; }
                     }
+                }
+            }
+            if (MOD | EQ | MINC) {
+                st[ST_MODIFIED] += __popc(MOD);
+                st[ST_SMOOTHED] += __popc(EQ);
+#pragma unroll
+                for (int w = 0; w < 4; w++) {
+                    const uint32_t q = qw[w];
+                    // rows of the min set whose quality is above the new one (both are below 128: bit 7 of the difference)
+                    const uint32_t lt = ~((nq[w] | 0x80808080u) - q) & 0x80808080u & expand4(MINC >> (4 * w));
+                    st[ST_SMOOTHED] += __popc(lt);
+                    const uint32_t take = expand4(EQ >> (4 * w)) | ((lt >> 7) * 0xFFu);
+                    qw[w] = (q & ~take) | (nq[w] & take) | (expand4(MOD >> (4 * w)) & 0x80808080u);
                 }
             }
         }
@@ -858,6 +913,7 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     cudaStream_t st = c->stream;
     if (n >= ((uint64_t)1 << 32) - 64) BFQ_FAIL(BFQ_ETOOLARGE, "BWT has %llu rows; this build indexes rows with 32 bits", (unsigned long long)n);
     if (P->max_len <= 0 || P->max_len > 255) BFQ_FAIL(BFQ_EINVAL, "max_len must be 1..255 (dataTypelenSeq is uchar, parameters.h:68)");
+    if (BFQ_M == 2 && P->default_q >= 128) BFQ_FAIL(BFQ_EINVAL, "default_q (-v) must be an ASCII quality below 128 (bit 7 of a stored quality marks a replaced base)");
 
     // ---- buildFreq (bfq_ext.cpp:132-187): symbol counts, alphabet in byte order, pile starts
     uint64_t hist[256], qhist[256];
@@ -875,6 +931,7 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     for (int b = 0; b < 256; b++) sc.byte2code[b] = A.byte2code[b] == 0xFF ? 0 : A.byte2code[b];
     memcpy(sc.code2byte, A.code2byte, 8);
     sc.K = P->K; sc.m = P->m; sc.qthr = P->qthr; sc.fthr = P->fthr;
+    sc.fT = (int32_t)std::min(1000.0f, std::max(-1000.0f, ceilf(P->fthr)));
     sc.default_q = P->default_q; sc.code_N = (int8_t)A.code_N; sc.acgt_mask = A.acgt_mask;
     sc.nsym = (uint8_t)A.nsym;
     sc.long_len = (uint32_t)std::min<int64_t>(c->opt_long_cluster, 4000);
