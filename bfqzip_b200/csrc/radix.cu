@@ -159,7 +159,8 @@ template <int B> __device__ __forceinline__ void match_bit(uint32_t d, uint32_t 
 // EMIT = true: the first pass of the flat-mode rebuild makes its input on the fly from the smoothed rows -- element i is
 // (text position SA[i] - 1, base | quality << 8), see PermSource in common.cuh -- so the pair list is never written
 // unsorted and read back (the loads are as many bytes as the pairs would be).
-template <typename K, typename V, typename S, int ITEMS, bool EMIT = false>
+// MB: digit bits the in-warp match looks at (8, or 6 for the passes of the permutation sort, whose digits have at most 6 bits)
+template <typename K, typename V, typename S, int ITEMS, bool EMIT = false, int MB = 8>
 __global__ void __launch_bounds__(RS_THREADS, RS_BLOCKS_PER_SM(ITEMS))
 rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
                    const V *__restrict__ vals_in, V *__restrict__ vals_out,
@@ -211,7 +212,8 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
         // (always all 8 digit bits: a pass with fewer bits has zeros above them, which match everywhere)
         uint32_t m = 0xffffffffu;
         match_bit<0>(d, m); match_bit<1>(d, m); match_bit<2>(d, m); match_bit<3>(d, m);
-        match_bit<4>(d, m); match_bit<5>(d, m); match_bit<6>(d, m); match_bit<7>(d, m);
+        match_bit<4>(d, m); match_bit<5>(d, m);
+        if constexpr (MB > 6) { match_bit<6>(d, m); match_bit<7>(d, m); }
         uint32_t prev = warp_cnt[w][d];
         __syncwarp();
         if ((__ffs(m) - 1) == lane) warp_cnt[w][d] = prev + __popc(m);
@@ -349,11 +351,23 @@ static int radix_passes(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals_b, 
             ProfScope ps(c, cls, 2 * n * (sizeof(K) + sizeof(V)));
             const size_t dyn = (size_t)TILE * sizeof(K);
             if constexpr (sizeof(K) == 4 && sizeof(V) == 2) {
+                if (!(src && p == 0) && P.bits[p] <= 6 && !wide) {          // a plain pass of the permutation sort: 6-bit match
+                    rs_onesweep_kernel<K, V, uint32_t, ITEMS, false, 6><<<tiles, RS_THREADS, dyn, c->stream>>>(
+                        kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX, (uint32_t *)status, tile_counter);
+                    BFQ_CUDA(cudaGetLastError());
+                    std::swap(kin, kout);
+                    std::swap(vin, vout);
+                    continue;
+                }
                 if (src && p == 0) {
                     if (wide)
                         rs_onesweep_kernel<K, V, uint64_t, ITEMS, true><<<tiles, RS_THREADS, dyn, c->stream>>>(
                             kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
                             (uint64_t *)status, tile_counter, *src);
+                    else if (P.bits[p] <= 6)
+                        rs_onesweep_kernel<K, V, uint32_t, ITEMS, true, 6><<<tiles, RS_THREADS, dyn, c->stream>>>(
+                            kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,
+                            (uint32_t *)status, tile_counter, *src);
                     else
                         rs_onesweep_kernel<K, V, uint32_t, ITEMS, true><<<tiles, RS_THREADS, dyn, c->stream>>>(
                             kin, kout, vin, vout, (uint32_t)n, P.shift[p], P.bits[p], hist + p * RS_RADIX,

@@ -587,7 +587,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     uint8_t *s_lcpout = s_rdepth + GT_S;                                            // [GT_S] LCP with the previous sorted row (staged part)
     uint64_t *s_refw = reinterpret_cast<uint64_t *>((reinterpret_cast<uintptr_t>(s_lcpout + GT_S) + 7) & ~(uintptr_t)7) +
                        (threadIdx.x >> 5) * GT_RW;                                  // [warps][GT_RW] words of the group's reference
-    __shared__ uint32_t s_ngroups, s_next;
+    __shared__ uint32_t s_ngroups, s_next, s_nsmall;     // s_ngroups: work items listed from the front, s_nsmall: small groups listed from the back
 
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t t0 = (A.tile0 + blockIdx.x) * (uint32_t)GT_T;
@@ -595,7 +595,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     const int ksym = A.ksym;
     const int depth = A.depth0 + ksym;
     const int kshift = 3 * ksym;                          // group id sits above the symbols (level >= 1)
-    if (tid == 0) { s_ngroups = 0; s_next = 0; }
+    if (tid == 0) { s_ngroups = 0; s_next = 0; s_nsmall = 0; }
 
     // ---- phase 0: the window's keys and positions come in with one batch of independent loads per thread (slot r of
     // the window sits at s_key[r + 1]; [0] is the key before the window, [GT_S + 1] the one after it), then the head
@@ -675,7 +675,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
                     }
                     if (size > 1) {
                         if (fits) {
-                            const uint32_t g = atomicAdd(&s_ngroups, 1u);
+                            // groups of more than 32 rows (the two-slot network, twice the work) are listed from the front and
+                            // handed out first, the others from the back: the warps finish closer together (longest first)
+                            const uint32_t g = size > 32 ? atomicAdd(&s_ngroups, 1u) : (uint32_t)GT_GMAX - 1u - atomicAdd(&s_nsmall, 1u);
                             s_gstart[g] = (uint16_t)gs; s_glen[g] = (uint16_t)size;
                         } else {
                             const uint32_t d = atomicAdd(A.defer_count, 1u);
@@ -703,9 +705,9 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     // ---- phase 1b: a tile of many small groups (low coverage) is cut into BATCHES instead -- batch i = the groups that
     // start in rows [i * GT_BATCH, (i + 1) * GT_BATCH) -- and a warp orders a whole batch at once.  Only the last group of a
     // batch can be longer than GT_BATCH rows; it becomes a work item of its own when the batch would exceed 64 rows.
-    if (s_ngroups > A.batch_min_groups) {                // (block-uniform)
+    if (s_ngroups + s_nsmall > A.batch_min_groups) {     // (block-uniform)
         __syncthreads();
-        if (tid == 0) s_ngroups = 0;
+        if (tid == 0) { s_ngroups = 0; s_nsmall = 0; }
         __syncthreads();
         constexpr int NBATCH = (GT_T + GT_BATCH - 1) / GT_BATCH;
         if (tid < NBATCH) {
@@ -731,12 +733,13 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     }
 
     // ---- phase 2: one warp orders one group (or one batch of small groups)
-    const uint32_t ngroups = s_ngroups;
+    const uint32_t nbig = s_ngroups, ngroups = nbig + s_nsmall;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&s_next, 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= ngroups) break;
+        if (g >= nbig) g = (uint32_t)GT_GMAX - 1u - (g - nbig);
         const uint32_t gs = s_gstart[g], len = s_glen[g] & 0x7FFFu;
         if (s_glen[g] & 0x8000u) {
             if (len <= 32) order_group_regs<1, true, P>(gs, len, lane, depth, A.T3, s_pos, s_len, s_best, s_sorted, s_lcpout, s_refw, s_gs);
