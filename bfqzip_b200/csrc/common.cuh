@@ -188,6 +188,7 @@ struct bfq_ctx {
     int64_t opt_flat_min_rows = 1 << 28;  // auto: flat mode from this many rows on
     int64_t opt_flat_min_rows_dev = 1 << 26;   // the same for device-resident calls (bfq_pipeline_dev)
     int opt_profile = 0;
+    int opt_bulk_tile = 1;                // group_tile_kernel phase 0 through cp.async.bulk (see sufsort.cu); 0 = per-thread loads
     int64_t opt_r11_cap = 0;              // test hook: first-attempt capacity of the two-base cluster list (0 = n / 8 + 1024)
     // accounting
     uint64_t launches = 0;

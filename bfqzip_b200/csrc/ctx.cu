@@ -245,6 +245,7 @@ int bfq_ctx_set_option(bfq_ctx *c, const char *key, int64_t value)
     else if (k == "flat_min_rows") { if (value < 0) { set_error("flat_min_rows must be >= 0"); return BFQ_EINVAL; } c->opt_flat_min_rows = value; }
     else if (k == "flat_min_rows_dev") { if (value < 0) { set_error("flat_min_rows_dev must be >= 0"); return BFQ_EINVAL; } c->opt_flat_min_rows_dev = value; }
     else if (k == "r11_cap") { if (value < 0) { set_error("r11_cap must be >= 0"); return BFQ_EINVAL; } c->opt_r11_cap = value; }
+    else if (k == "bulk_tile") c->opt_bulk_tile = value ? 1 : 0;
     else if (k == "profile") c->opt_profile = value ? 1 : 0;
     else if (k == "trace") c->opt_trace = value ? 1 : 0;
     else if (k == "wide_positions") c->opt_wide_positions = value ? 1 : 0;

@@ -192,6 +192,7 @@ struct GroupTileArgsT {
     int embed;                  // level 0, k <= 16: key bits 63..48 hold QL[pos]
     uint32_t group_cap;         // groups with more members are deferred even when they fit (test hook)
     uint32_t batch_min_groups;  // tiles with more groups than this are ordered batch-wise
+    int bulk_tile;              // phase 0: the window comes in with two cp.async.bulk copies (mbarrier completion) instead of per-thread loads
 };
 using GroupTileArgs = GroupTileArgsT<uint32_t>;
 
@@ -572,8 +573,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1280 / GT_THREADS)
 group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 {
     extern __shared__ __align__(16) unsigned char gt_smem[];
-    uint64_t *s_key = reinterpret_cast<uint64_t *>(gt_smem);                        // [GT_S] keys of groups > 64 rows
-    P *s_pos = reinterpret_cast<P *>(s_key + GT_S + 2);                                 // [GT_S] text position of the row's suffix
+    uint64_t *s_key = reinterpret_cast<uint64_t *>(gt_smem) + 1;                    // [GT_S + 2]; &s_key[1] is 16-byte aligned (bulk copy target)
+    P *s_pos = reinterpret_cast<P *>(s_key + GT_S + 3);                                 // [GT_S] text position of the row's suffix (16-byte aligned)
     uint32_t *s_best = reinterpret_cast<uint32_t *>(s_pos + GT_S);                                                // [GT_S] (length << 16 | row) of a run's reference
     uint32_t *s_head = s_best + GT_S;                                               // [GT_HW]
     uint16_t *s_prev = reinterpret_cast<uint16_t *>(s_head + GT_HW);                // [GT_S] previous symbol code | its quality << 8
@@ -600,7 +601,33 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
     // ---- phase 0: the window's keys and positions come in with one batch of independent loads per thread (slot r of
     // the window sits at s_key[r + 1]; [0] is the key before the window, [GT_S + 1] the one after it), then the head
     // bitmap: bit r <=> list slot t0 + r starts a group
-    {
+    __shared__ __align__(8) uint64_t s_bar;
+    const bool bulk = A.bulk_tile && sizeof(K) == 8 && (uint64_t)t0 + GT_S <= m;      // a full window: sizes are multiples of 16 bytes
+    if (bulk) {
+        // Blackwell/Hopper bulk asynchronous copy (SASS UBLKCP): ONE thread moves the window's keys (10 KB) and positions
+        // straight into shared memory; the copy engine signals the mbarrier with the byte count.  No thread stages data
+        // through registers (the per-thread path below holds 15 registers and issues 10 loads + 10 shared stores).
+        const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&s_bar);
+        if (tid == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncthreads();
+        if (tid == 0) {
+            constexpr uint32_t kbytes = GT_S * sizeof(K), pbytes = GT_S * sizeof(P);
+            uint64_t pol;
+            asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));      // the list streams through once
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kbytes + pbytes) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(s_key + 1)), "l"(keys + t0), "r"(kbytes), "r"(bar), "l"(pol) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                         ::"r"((uint32_t)__cvta_generic_to_shared(s_pos)), "l"(A.pos + t0), "r"(pbytes), "r"(bar), "l"(pol) : "memory");
+            s_key[0] = t0 > 0 ? keys[t0 - 1] : (K)0;
+        }
+        if (tid == 32) s_key[GT_S + 1] = (uint64_t)t0 + GT_S < m ? keys[(uint64_t)t0 + GT_S] : (K)0;
+        asm volatile("{\n\t.reg .pred p;\n\tBULK_WAIT:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], 0;\n\t@p bra BULK_DONE;\n\tbra BULK_WAIT;\n\tBULK_DONE:\n\t}"
+                     ::"r"(bar) : "memory");
+    } else {
         constexpr int NB = (GT_S + GT_THREADS - 1) / GT_THREADS;
         K kk[NB]; P pp[NB];
 #pragma unroll
@@ -772,7 +799,7 @@ group_tile_kernel(const K *__restrict__ keys, GroupTileArgsT<P> A)
 
 static size_t group_tile_smem(size_t pos_bytes)
 {
-    return (size_t)(GT_S + 2) * 8 + (size_t)GT_S * (4 + pos_bytes) + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
+    return (size_t)(GT_S + 4) * 8 + (size_t)GT_S * (4 + pos_bytes) + (size_t)GT_HW * 4 + (size_t)GT_S * 2 * 4 + (size_t)GT_GMAX * 2 * 2 +
            (size_t)GT_S * 3 + (size_t)(GT_THREADS / 32) * GT_RW * 8 + 8 + 16;
 }
 
@@ -1004,6 +1031,7 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
     G.code2byte = c2b; G.eos = eos; G.defer_count = dcount; G.defer_cap = dcap;
     G.group_cap = (uint32_t)c->opt_group_cap;
     G.batch_min_groups = (uint32_t)c->opt_batch_min_groups;
+    G.bulk_tile = c->opt_bulk_tile;
     G.prev_key = prev_key; G.has_prev = has_prev;
 
     int parity = 0, depth = 0, ksym = k, level = 0;

@@ -376,3 +376,21 @@ def test_fused_calls_refuse_reads_longer_than_max_len():
     # and the context is usable afterwards
     (b2, q2, l2), _, _ = c.pipeline(bases, quals, off, lib.default_params(eos=35, max_len=250))
     assert np.array_equal(b2, bwt)
+
+
+@pytest.mark.parametrize("bulk", [0, 1])
+def test_part_a_tile_load_paths(bulk):
+    """group_tile_kernel brings a window's keys and positions in either with two cp.async.bulk copies (mbarrier completion,
+    the default) or with per-thread loads (the last, partial windows always do): both must give the reference's rows."""
+    g = np.load(os.path.join(H.GOLDEN, "syn_fixed.npz"))
+    bases, quals, off = synth.make_reads(30000, 100, 31337)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    c = ctx()
+    c.set_option("bulk_tile", bulk)
+    try:
+        bwt, qs, lcp = c.build_ebwt(g["bases"], g["quals"], g["off"], 35)
+        b2, q2, l2 = c.build_ebwt(bases, quals, off, 35)
+    finally:
+        c.set_option("bulk_tile", 1)
+    assert np.array_equal(bwt, g["bwt"]) and np.array_equal(qs, g["qs"]) and np.array_equal(lcp, g["lcp"])
+    assert np.array_equal(b2, rb) and np.array_equal(q2, rq) and np.array_equal(l2, rl)
