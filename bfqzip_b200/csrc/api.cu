@@ -365,7 +365,9 @@ int bfq_dist_build(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals,
     if (params->K < 4) BFQ_FAIL(BFQ_EINVAL, "single-collection mode over several GPUs needs -k >= 4 (ranges are cut on 4 symbols)");
     bfq_ctx *c = ctx;
     uint64_t mn, mx;
+    c->trace("dist_build: call start", c->stream);
     check_reads_dev(c, d_off, nreads, total_bases, &mn, &mx);
+    c->trace("dist_build: reads checked", c->stream);
     if (mx > (uint64_t)params->max_len) BFQ_FAIL(BFQ_EINVAL, "a read has %llu symbols, -l is %d", (unsigned long long)mx, params->max_len);
     const uint64_t N = total_bases + nreads;
     if (stats) memset(stats, 0, sizeof *stats);
@@ -386,16 +388,20 @@ int bfq_dist_build(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_quals,
         c->arena.release(mk);
     }
     *n_local = R.n_local; *row_base = R.row_base;
+    c->trace("dist_build: slice of the eBWT built", c->stream);
     if (R.n_local) {
         uint64_t ah[256];
         memcpy(ah, c->base_hist, sizeof ah);
         ah[params->eos_byte] += nreads;
         SmoothResult S;
         smooth_dev(c, d_bwt, d_qs, d_lcp, R.n_local, params, &S, stats, d_sa, d_t3, ah, wide);
+        c->trace("dist_build: slice smoothed", c->stream);
         emit_sorted_pairs_dev(c, S, d_bwt, d_sa, wide, N, text_bounds, world, d_keys, d_vals, send_counts);
+        c->trace("dist_build: pairs grouped by destination", c->stream);
     }
     if (stats) { stats->n = N; stats->nreads = nreads; }
     BFQ_CUDA(cudaStreamSynchronize(c->stream));
+    c->trace_dump();
     API_END
 }
 

@@ -966,6 +966,7 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
     // ---- alphabet from the data (codes follow byte order, like gsufsort's +1 remap)
     uint64_t hist[256];
     byte_histogram(c, d_bases, total_bases, hist);
+    c->trace("part A: byte histogram", st);
     memcpy(c->base_hist, hist, sizeof hist);
     Alphabet A = alphabet_from_hist(hist, eos, /*eos_may_appear=*/false);
     // gsufsort drops bytes <= 1 and 255 (utils.c:229-236); refuse them instead of silently differing
@@ -1048,6 +1049,7 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
         launch_group_tile<uint64_t, P>(c, keys, G);
         fetch_small(c, c->h_small, dcount, 4);
         BFQ_CUDA(cudaStreamSynchronize(st));
+        c->trace("part A: groups of a level ordered", st);
         const uint32_t ndef = ((uint32_t *)c->h_small)[0];
         if (ndef == 0) break;
         if (c->sink) c->sink->files_copied = false;      // deferred groups rewrite rows that already left
