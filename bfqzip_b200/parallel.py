@@ -11,9 +11,8 @@ Mirrors (reference file:line):
 The result depends on the number of BLOCKS, never on the number of GPUs: blocks are dealt to
 ranks in contiguous runs and every block is an independent collection with its own eBWT.
 
-Ranks are ``torch.distributed`` processes (one per GPU, NCCL for device work; the host-side
-gather of finished blocks goes through a gloo group, or through per-block files like the
-reference's ``cat``).  Nothing here touches the GPU itself: ``process_block`` does.
+Ranks are ``torch.distributed`` processes (one per GPU).  Finished blocks reach rank 0 through per-block
+files like the reference's ``cat`` (``spill_dir``), or -- small inputs only -- through a gloo ``gather_object``.  Nothing here touches the GPU itself: ``process_block`` does.
 """
 from __future__ import annotations
 
@@ -91,16 +90,43 @@ def merge_blocks(done: Sequence[Tuple[Reads, int]], paired: bool):
     return concat_reads(m1), concat_reads(m2)
 
 
+def _spill_paths(spill_dir: str, b: int):
+    import os
+    return [os.path.join(spill_dir, f"block_{b:05d}.{e}") for e in ("bases", "quals", "off")]
+
+
 def run_blocks(reads1: Reads, threads: int, process_block: Callable[[Reads], Reads],
-               reads2: Reads | None = None, rank: int = 0, world: int = 1, gather_group=None):
+               reads2: Reads | None = None, rank: int = 0, world: int = 1, gather_group=None, spill_dir: str | None = None):
     """Every rank processes its run of blocks; rank 0 returns the merged result, others None.
 
     ``process_block`` maps one block (bases, quals, off) to (out_bases, out_quals, out_off); on a GPU
-    rank it is ``BfqGpu.pipeline`` of that rank's context.  ``gather_group`` is a host-side
-    (gloo) process group used only to bring finished blocks to rank 0.
+    rank it is ``BfqGpu.pipeline`` of that rank's context.  Finished blocks reach rank 0 in one of two ways:
+
+    * ``spill_dir`` (a directory every rank of the node sees): each rank writes its blocks as three raw files per block and
+      rank 0 memory-maps them after a barrier on ``gather_group`` -- what the reference does with its per-block output files
+      and ``cat`` (BFQzip_parallel.py:153-177).  This is the path for real sizes: a config-4 run moves 12 GB of reads.
+    * no ``spill_dir``: ``gather_object`` on ``gather_group`` (pickled arrays through gloo; fine for small inputs and tests).
     """
     blocks = make_blocks(reads1, threads, reads2)
     mine = blocks_of_rank(len(blocks), rank, world)
+    if spill_dir is not None and world > 1:
+        import os
+        import torch.distributed as dist
+        os.makedirs(spill_dir, exist_ok=True)
+        for b in mine:
+            out = process_block(blocks[b][0])
+            for path, arr, dt in zip(_spill_paths(spill_dir, b), out, (np.uint8, np.uint8, np.uint64)):
+                np.ascontiguousarray(arr, dt).tofile(path)
+        dist.barrier(group=gather_group)                  # every block file is complete
+        if rank != 0:
+            return None
+        everything = []
+        for b in range(len(blocks)):
+            pb, pq, po = _spill_paths(spill_dir, b)
+            off = np.fromfile(po, np.uint64)
+            rd = lambda path: np.memmap(path, np.uint8, "r") if os.path.getsize(path) else np.empty(0, np.uint8)
+            everything.append((b, (rd(pb), rd(pq), off)))
+        return merge_blocks([(out, blocks[b][1]) for b, out in everything], reads2 is not None)
     local = [(b, process_block(blocks[b][0])) for b in mine]
     if world == 1:
         everything = local

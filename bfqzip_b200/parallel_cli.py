@@ -113,7 +113,11 @@ def main(argv=None):
         _, (ob, oq), _ = g.pipeline(block[0], block[1], block[2], P, want_files=False)
         return ob, oq, block[2]
 
-    merged = parallel.run_blocks(reads1, args.threads, gpu_block, reads2, rank=rank, world=world, gather_group=group)
+    # several ranks: finished blocks go through per-block files next to the output (removed afterwards), not through pickles
+    spill = None
+    if world > 1:
+        spill = os.path.join(os.path.dirname(os.path.abspath(output_names(args)[0])), ".bfq_blocks_" + os.environ.get("MASTER_PORT", "0"))
+    merged = parallel.run_blocks(reads1, args.threads, gpu_block, reads2, rank=rank, world=world, gather_group=group, spill_dir=spill)
     g.close()
     if rank == 0:
         names = output_names(args)
@@ -126,8 +130,11 @@ def main(argv=None):
             print("step 5 (PPMd / BSC entropy coding) stays on the host and is not run by this launcher; "
                   "pass the merged files to the reference's compressors")
     if world > 1:
+        import shutil
         import torch.distributed as dist
         dist.barrier()
+        if rank == 0 and spill:
+            shutil.rmtree(spill, ignore_errors=True)
         dist.destroy_process_group()
     return 0
 

@@ -78,18 +78,29 @@ def _worker(rank, world, port, q):
         r2 = synth.make_reads(203, 40, 6, var_len=True)
         single = parallel.run_blocks(r1, 8, _tag, rank=rank, world=world)
         paired = parallel.run_blocks(r1, 8, _tag, r2, rank=rank, world=world)
+        # the per-block-file path (what real sizes use) must give the same merged collections as the pickled gather
+        spill = os.path.join(os.environ["BFQ_TEST_SPILL"], "blocks")
+        single_f = parallel.run_blocks(r1, 8, _tag, rank=rank, world=world, spill_dir=spill + "_s")
+        paired_f = parallel.run_blocks(r1, 8, _tag, r2, rank=rank, world=world, spill_dir=spill + "_p")
         if rank == 0:
+            for a, b in zip(single, single_f):
+                assert np.array_equal(a, np.asarray(b))
+            for ma, mb in zip(paired, paired_f):
+                for a, b in zip(ma, mb):
+                    assert np.array_equal(a, np.asarray(b))
+            assert len(os.listdir(spill + "_p")) == 3 * 8
             q.put((single, paired))
         else:
-            assert single is None and paired is None
+            assert single is None and paired is None and single_f is None and paired_f is None
         dist.barrier()
     finally:
         dist.destroy_process_group()
 
 
-def test_two_ranks_gloo_equal_one_rank():
-    """The result depends on the block count, not on the rank count."""
+def test_two_ranks_gloo_equal_one_rank(tmp_path, monkeypatch):
+    """The result depends on the block count, not on the rank count -- through both gather paths."""
     import torch.multiprocessing as mp
+    monkeypatch.setenv("BFQ_TEST_SPILL", str(tmp_path))
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
