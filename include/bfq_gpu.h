@@ -2,7 +2,7 @@
  *
  * The reference has no in-process API for this path: BFQzip_ext.py runs two tools as
  * subprocesses and exchanges flat files (BFQzip_ext.py:173-177, 207-215, 310-318).  The
- * entry points below are what the two drop-in tools (tools/gsufsort_gpu.cpp, tools/bfq_ext_gpu.cpp)
+ * entry points below are what the two drop-in tools (tools/step1_main.cpp, tools/bfq_ext_main.cpp)
  * bind, and what a maintainer would bind from the reference's own C/C++ tools:
  *
  *   bfq_build_ebwt      replaces  gsufsort's load + cat_all + gsacak + store_to_disk
@@ -134,9 +134,13 @@ int bfq_pipeline_dev(bfq_ctx *ctx, const uint8_t *d_bases, const uint8_t *d_qual
  * The same three calls with the FASTQ file contents on either side instead of flat arrays: the
  * newline scan and field split of the loaders (external/gsufsort/lib/file.c:182-275 keeps line 2
  * and line 4 of every 4-line record; empty reads are dropped, lib/utils.c:229-236; a trailing
- * partial record is ignored; '\r' before '\n' is stripped) and the record writer of step 3
+ * partial record is ignored) and the record writer of step 3
  * (src_ext_mem/decode.cpp:1080-1127: "@\nBASES\n+\nQUALS\n", header "@" alone -- use the flat calls
  * for -H header files) run on the device.  text: host pointer (pageable or pinned) to `size` bytes.
+ * REPO-DEFINED, not the reference's behaviour: a '\r' before '\n' is stripped and a last line without '\n' is kept
+ * whole.  The reference's loader overwrites the LAST byte of every line it reads (lib/file.c:210-212), so it keeps '\r'
+ * as a symbol of the read and cuts the final symbol off an unterminated last line; parity is claimed on LF-terminated
+ * files only.
  * bwt/qs/lcp hold `capacity` bytes each; size / 2 always suffices.  The FASTQ written for a
  * collection of R reads and T bases takes 2 T + 6 R bytes; `size` always suffices when it is the
  * text the reads came from.  Errors: BFQ_EINVAL for a record whose two payload lines differ in
