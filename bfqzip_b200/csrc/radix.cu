@@ -190,6 +190,19 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
     const uint32_t tile = s_tile;
     const uint32_t tile_base = tile * (uint32_t)TILE;
     const uint32_t valid = min((uint32_t)TILE, n - tile_base);
+    // EMIT: the tile's stored-quality and BWT bytes are contiguous -- the block fetches them with 16-byte loads (one per thread
+    // and array for a 4096-row tile) into shared memory instead of 2 * ITEMS one-byte loads per thread
+    __shared__ __align__(16) uint8_t s_emit[EMIT ? 2 * TILE : 16];
+    bool emit_staged = false;
+    if constexpr (EMIT) {
+        emit_staged = valid == (uint32_t)TILE && ((reinterpret_cast<uintptr_t>(src.qflat) | reinterpret_cast<uintptr_t>(src.bwt)) & 15) == 0;
+        if (emit_staged) {
+            for (int i = tid; i < TILE / 16; i += RS_THREADS) {
+                reinterpret_cast<uint4 *>(s_emit)[i] = __ldcs(reinterpret_cast<const uint4 *>(src.qflat + tile_base) + i);
+                reinterpret_cast<uint4 *>(s_emit + TILE)[i] = __ldcs(reinterpret_cast<const uint4 *>(src.bwt + tile_base) + i);
+            }
+        }
+    }
 
     // ---- load keys (warp-striped: item i of lane l sits at warp_base + i*32 + l)
     K key[ITEMS];
@@ -272,9 +285,12 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
         if constexpr (EMIT) {
             val[i] = (V)0;
             if (loc < valid) {
+                // both bytes are loaded unconditionally (independent loads, all 2 * ITEMS of them in flight); only the rare
+                // rows whose base was replaced (bit 7) touch obase
                 const uint32_t r = tile_base + loc;
-                const uint8_t q = src.qflat[r];
-                const uint8_t base = (q & 0x80) ? src.obase[r] : src.bwt[r];
+                const uint8_t q = emit_staged ? s_emit[loc] : __ldcs(src.qflat + r);      // (staged before the first barrier)
+                uint8_t base = emit_staged ? s_emit[TILE + loc] : __ldcs(src.bwt + r);
+                if (q & 0x80) base = src.obase[r];
                 val[i] = (V)(base | ((uint32_t)(q & 0x7F) << 8));
             }
         } else
