@@ -84,7 +84,9 @@ rs_hist_kernel(const K *__restrict__ keys, uint64_t n, RsPasses P, uint32_t *__r
     }
 }
 
-// level-0 suffix keys + their digit histograms in one pass over the packed text (see common.cuh)
+// level-0 suffix keys + their digit histograms in one pass over the packed text (see common.cuh).
+// A thread takes FOUR consecutive text positions per step: their windows lie in three consecutive words of the packed
+// text (loaded once), their QL entries are one 8-byte load, and the four keys / positions leave as 16-byte stores.
 __global__ void __launch_bounds__(RS_THREADS)
 rs_suffix_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k, RsPasses P,
                       uint64_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t *__restrict__ hist)
@@ -93,18 +95,51 @@ rs_suffix_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restric
     for (int i = threadIdx.x; i < 2 * RS_MAX_PASSES * RS_RADIX; i += RS_THREADS) (&sh[0][0][0])[i] = 0;
     __syncthreads();
     const int copy = (threadIdx.x >> 5) & 1;
-    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
-    for (uint64_t p = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; p < n; p += stride) {
-        uint64_t w = text_window(T3, p);
-        const int f = leading_nonzero_fields(w);          // symbols before the first terminator
-        if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
-        uint64_t key = w >> (64 - 3 * k);
+    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS * 4;
+    const bool vec = ((reinterpret_cast<uintptr_t>(keys) | reinterpret_cast<uintptr_t>(vals)) & 15) == 0 &&
+                     (!QL || (reinterpret_cast<uintptr_t>(QL) & 7) == 0);
+    for (uint64_t p0 = ((uint64_t)blockIdx.x * RS_THREADS + threadIdx.x) * 4; p0 < n; p0 += stride) {
+        const uint64_t bit = 3 * p0;
+        const uint64_t wi = bit >> 6;
+        const int s0 = (int)(bit & 63);
+        const uint64_t w0 = T3[wi], w1 = T3[wi + 1], w2 = T3[wi + 2];     // (the text is padded: windows past the end read zeros)
+        const bool full = vec && p0 + 4 <= n;
+        uint32_t ql[4] = {0, 0, 0, 0};
+        if (QL) {
+            if (full) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(QL + p0);
+                ql[0] = v.x & 0xFFFFu; ql[1] = v.x >> 16; ql[2] = v.y & 0xFFFFu; ql[3] = v.y >> 16;
+            } else {
 #pragma unroll
-        for (int q = 0; q < RS_MAX_PASSES; q++)
-            if (q < P.num) atomicAdd(&sh[copy][q][digit_of(key, P.shift[q], (1u << P.bits[q]) - 1)], 1u);
-        if (QL) key |= (uint64_t)QL[p] << 48;             // rides in bits the sort ignores (k <= 16)
-        keys[p] = key;
-        vals[p] = (uint32_t)p;
+                for (int i = 0; i < 4; i++) if (p0 + i < n) ql[i] = QL[p0 + i];
+            }
+        }
+        uint64_t key[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int s = s0 + 3 * i;                                        // < 73
+            uint64_t w;
+            if (s < 64) w = s ? ((w0 << s) | (w1 >> (64 - s))) : w0;
+            else { const int t = s - 64; w = t ? ((w1 << t) | (w2 >> (64 - t))) : w1; }
+            w &= ~1ull;
+            const int f = leading_nonzero_fields(w);          // symbols before the first terminator
+            if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
+            const uint64_t kk = w >> (64 - 3 * k);
+            if (p0 + i < n) {
+#pragma unroll
+                for (int q = 0; q < RS_MAX_PASSES; q++)
+                    if (q < P.num) atomicAdd(&sh[copy][q][digit_of(kk, P.shift[q], (1u << P.bits[q]) - 1)], 1u);
+            }
+            key[i] = kk | ((uint64_t)ql[i] << 48);            // QL rides in bits the sort ignores (k <= 16); 0 without QL
+        }
+        if (full) {
+            *reinterpret_cast<ulonglong2 *>(keys + p0) = make_ulonglong2(key[0], key[1]);
+            *reinterpret_cast<ulonglong2 *>(keys + p0 + 2) = make_ulonglong2(key[2], key[3]);
+            *reinterpret_cast<uint4 *>(vals + p0) = make_uint4((uint32_t)p0, (uint32_t)p0 + 1, (uint32_t)p0 + 2, (uint32_t)p0 + 3);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; i++) if (p0 + i < n) { keys[p0 + i] = key[i]; vals[p0 + i] = (uint32_t)(p0 + i); }
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < P.num * RS_RADIX; i += RS_THREADS) {
@@ -640,7 +675,7 @@ int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, u
     BFQ_CUDA(cudaMemsetAsync(hist, 0, RS_MAX_PASSES * RS_RADIX * sizeof(uint32_t), c->stream));
     {
         ProfScope ps(c, PC_KEYS, n * (8 + 4 + 2) + n * 3 / 8);
-        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS));
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS * 4));
         rs_suffix_keys_kernel<<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
         BFQ_CUDA(cudaGetLastError());
     }
