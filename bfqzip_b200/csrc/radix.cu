@@ -479,9 +479,23 @@ __device__ __forceinline__ uint64_t suffix_key(const uint64_t *__restrict__ T3, 
     return w >> (64 - 3 * k);
 }
 
+// the same key for a window that starts `s` bits (s < 128) into three consecutive words of the packed text: consecutive
+// positions share the words, so a thread that takes a run of positions loads them once
+__device__ __forceinline__ uint64_t suffix_key3(uint64_t w0, uint64_t w1, uint64_t w2, int s, int k)
+{
+    uint64_t w;
+    if (s < 64) w = s ? ((w0 << s) | (w1 >> (64 - s))) : w0;
+    else { const int t = s - 64; w = t ? ((w1 << t) | (w2 >> (64 - t))) : w1; }
+    w &= ~1ull;
+    const int f = leading_nonzero_fields(w);          // symbols before the first terminator
+    if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
+    return w >> (64 - 3 * k);
+}
+
 constexpr int RS_TOP_BITS = 12;
 constexpr int RS_SEL_ITEMS = 16;                      // consecutive positions per thread in the selection kernels
 constexpr int RS_SEL_CHUNK = RS_THREADS * RS_SEL_ITEMS;
+static_assert(3 * (RS_SEL_ITEMS - 1) + 63 + 63 < 192, "the windows of a thread's run of positions lie in three words");
 
 __global__ void __launch_bounds__(RS_THREADS)
 rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint64_t n, int k, uint32_t *__restrict__ hist)
@@ -489,9 +503,15 @@ rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint64_t n, int k, uint32_t 
     __shared__ uint32_t sh[1 << RS_TOP_BITS];
     for (int i = threadIdx.x; i < (1 << RS_TOP_BITS); i += RS_THREADS) sh[i] = 0;
     __syncthreads();
-    const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
-    for (uint64_t p = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; p < n; p += stride)
-        atomicAdd(&sh[(uint32_t)(suffix_key(T3, p, k) >> (3 * k - RS_TOP_BITS))], 1u);
+    const uint64_t stride = (uint64_t)gridDim.x * RS_SEL_CHUNK;
+    for (uint64_t p0 = ((uint64_t)blockIdx.x * RS_THREADS + threadIdx.x) * RS_SEL_ITEMS; p0 < n; p0 += stride) {
+        const uint64_t bit = 3 * p0, wi = bit >> 6;
+        const int s0 = (int)(bit & 63);
+        const uint64_t w0 = T3[wi], w1 = T3[wi + 1], w2 = T3[wi + 2];      // 16 windows: 3 * 15 + 63 + s0 < 192 bits
+#pragma unroll
+        for (int i = 0; i < RS_SEL_ITEMS; i++)
+            if (p0 + i < n) atomicAdd(&sh[(uint32_t)(suffix_key3(w0, w1, w2, s0 + 3 * i, k) >> (3 * k - RS_TOP_BITS))], 1u);
+    }
     __syncthreads();
     for (int i = threadIdx.x; i < (1 << RS_TOP_BITS); i += RS_THREADS)
         if (sh[i]) atomicAdd(&hist[i], sh[i]);
@@ -514,12 +534,15 @@ rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ Q
     uint64_t key[RS_SEL_ITEMS];
     uint32_t mine = 0;
     unsigned long long below = 0; bool any_below = false;
+    uint64_t w0 = 0, w1 = 0, w2 = 0;
+    const int s0 = (int)((3 * p0) & 63);
+    if (p0 < n) { const uint64_t wi = (3 * p0) >> 6; w0 = T3[wi]; w1 = T3[wi + 1]; w2 = T3[wi + 2]; }
 #pragma unroll
     for (int i = 0; i < RS_SEL_ITEMS; i++) {
         const uint64_t p = p0 + i;
         key[i] = ~0ull;
         if (p < n) {
-            const uint64_t kk = suffix_key(T3, p, k);
+            const uint64_t kk = suffix_key3(w0, w1, w2, s0 + 3 * i, k);
             if (kk >= lo && kk < hi) { key[i] = kk; mine++; }
             else if (!WRITE && kk < lo) { below = max(below, (unsigned long long)kk); any_below = true; }
         }
