@@ -218,6 +218,24 @@ class BfqGpu:
         files = (bwt[:k], qs[:k], lcp[:k]) if want_files else None
         return files, out[:int(size.value)].tobytes(), st.as_dict()
 
+    # ---- quality-stream pre-transform for the host entropy coders
+    def qs_rle_encode(self, qs: bytes | np.ndarray):
+        """The step-4 quality stream (one line per read) -> (run values, run lengths), two uint8 arrays of equal length."""
+        buf = np.frombuffer(qs, np.uint8) if isinstance(qs, (bytes, bytearray)) else np.ascontiguousarray(qs, np.uint8)
+        n = len(buf)
+        vals = np.empty(max(n, 1), np.uint8); lens = np.empty(max(n, 1), np.uint8)
+        nruns = C.c_uint64(0)
+        self._chk(self.lib.bfq_qs_rle_encode(self.h, _ptr(buf), C.c_uint64(n), _ptr(vals), _ptr(lens), C.c_uint64(n), C.byref(nruns)))
+        return vals[:int(nruns.value)], lens[:int(nruns.value)]
+
+    def qs_rle_decode(self, vals, lens, capacity: int | None = None):
+        vals = np.ascontiguousarray(vals, np.uint8); lens = np.ascontiguousarray(lens, np.uint8)
+        cap = int(lens.astype(np.uint64).sum()) if capacity is None else capacity
+        out = np.empty(max(cap, 1), np.uint8)
+        n = C.c_uint64(0)
+        self._chk(self.lib.bfq_qs_rle_decode(self.h, _ptr(vals), _ptr(lens), C.c_uint64(len(vals)), _ptr(out), C.c_uint64(cap), C.byref(n)))
+        return out[:int(n.value)]
+
     # ---- one collection over several GPUs (bfq_dist_build / bfq_dist_place)
     def dist_build(self, d_bases, d_quals, d_off, nreads, total_bases, params: Params, rank, world, capacity,
                    text_bounds, d_bwt, d_qs, d_lcp, d_keys, d_vals):

@@ -199,6 +199,19 @@ void bfq_prof_reset(bfq_ctx *ctx);
 /* number of kernel launches issued by this ctx since creation (bench.py's gpu_launches) */
 uint64_t bfq_launch_count(bfq_ctx *ctx);
 
+/* ---- quality-stream pre-transform for the host entropy coders --------------------
+ * The stream of step 4 (BFQzip_ext.py:224-244: `sed -n 4~4p OUT.fq`, one line of qualities per read; what `bfq_ext -C`
+ * writes as OUT.fq.qs) as two byte streams of equal length: run values and run lengths.  After smoothing the stream is
+ * dominated by runs of the clusters' new quality; the reference hands it to 7z PPMd / bsc unchanged
+ * (BFQzip_ext.py:248-272) -- this transform is optional, invertible and changes no file contract.
+ * Defined on newline-separated lines of at most 255 symbols: a run never exceeds 255 bytes (BFQ_EINVAL otherwise).
+ *   encode: qs[n] -> vals[*nruns], lens[*nruns]   (capacity = bytes available in each output; n always suffices)
+ *   decode: the inverse; qs holds `capacity` bytes, *n = bytes written.   Host buffers; n and nruns below 2^32. */
+int bfq_qs_rle_encode(bfq_ctx *ctx, const uint8_t *qs, uint64_t n, uint8_t *vals, uint8_t *lens, uint64_t capacity,
+                      uint64_t *nruns);
+int bfq_qs_rle_decode(bfq_ctx *ctx, const uint8_t *vals, const uint8_t *lens, uint64_t nruns, uint8_t *qs,
+                      uint64_t capacity, uint64_t *n);
+
 /* ---- allocation-free entry point ------------------------------------------------------- */
 /* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).

@@ -152,3 +152,17 @@ def ref_bfq_ext(bwt, qs, lcp, M=2, B=0, eos=35, K=None, m=5, v=None, headers=Non
         return fq, parse_ref_stats(r.stdout.decode("latin1"))
     finally:
         shutil.rmtree(wd, ignore_errors=True)
+
+
+# ------------------------------------------------------------------ quality-stream pre-transform
+def rle_encode_numpy(stream: np.ndarray):
+    """CPU restatement of bfq_qs_rle_encode, numpy: maximal runs of equal bytes -> (values, lengths).  Test infrastructure:
+    there is no counterpart in the reference (its step 5 takes the stream as it is, BFQzip_ext.py:248-272), so the checker
+    is this restatement plus the round trip."""
+    stream = np.ascontiguousarray(stream, np.uint8)
+    if stream.size == 0:
+        return np.empty(0, np.uint8), np.empty(0, np.uint8)
+    heads = np.flatnonzero(np.concatenate([[True], stream[1:] != stream[:-1]]))
+    lens = np.diff(np.concatenate([heads, [stream.size]]))
+    assert lens.max() <= 255
+    return stream[heads], lens.astype(np.uint8)

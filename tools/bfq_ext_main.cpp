@@ -40,6 +40,8 @@ static void help()
          << "-s <arg>    ASCII value of end-marker symbol. Default: 35 (#)." << endl
          << "-T <arg>    Number of threads (ignored: the work runs on the GPU). Default: 1." << endl
          << "-G <arg>    CUDA device index. Default: 0." << endl
+         << "-C          Also write OUT.fq.dna and OUT.fq.qs (the streams of the driver's step 4)." << endl
+         << "-R          -C plus OUT.fq.qs.rlv / OUT.fq.qs.rll: run values and run lengths of OUT.fq.qs." << endl
          << "-H <arg>    Original headers from file." << endl
          << endl
          << "GPU build (sm_100a), mode M=" << bfq_mode_M() << " B=" << bfq_mode_B() << "." << endl;
@@ -61,9 +63,9 @@ int main(int argc, char **argv)
     char default_value = '\0';
     float fthr = 0.0f;
     char TERM = '#';
-    bool components = false;
+    bool components = false, rle = false;
     int opt;
-    while ((opt = getopt(argc, argv, "he:q:o:a:l:k:m:v:f:t:s:T:H:G:DVC")) != -1) {
+    while ((opt = getopt(argc, argv, "he:q:o:a:l:k:m:v:f:t:s:T:H:G:DVCR")) != -1) {
         switch (opt) {
         case 'h': help(); break;
         case 'e': input_dna = optarg; break;
@@ -82,6 +84,7 @@ int main(int argc, char **argv)
         case 'H': input_titles = optarg; headers = true; break;
         case 'D': case 'V': break;
         case 'C': components = true; break;                     // extension: also write OUT.fq.dna / OUT.fq.qs (step 4's streams)
+        case 'R': components = true; rle = true; break;         // extension: -C plus the run-length form of OUT.fq.qs (.rlv values, .rll lengths)
         default: help(); return -1;
         }
     }
@@ -147,6 +150,17 @@ int main(int argc, char **argv)
                                                         components ? dna.get() : nullptr, components ? qsl.get() : nullptr, &S)
                              : bfq_smooth_rebuild(ctx, fb.data, fq.data, fl.data, n, &P, ob.get(), oq.get(), off.data(), nreads + 1, &S);
         if (rc != BFQ_OK) { std::cerr << "Error: " << bfq_last_error() << endl; bfq_ctx_destroy(ctx); return EXIT_FAILURE; }
+        // pre-transform for the host entropy coders, while the context is alive: run values and run
+        // lengths of the quality stream (text = 2 T + 6 R bytes; the stream holds T + R)
+        std::unique_ptr<uint8_t[]> rv, rl;
+        uint64_t nruns = 0;
+        if (rle) {
+            const uint64_t k = (text_size - 6 * S.nreads) / 2 + S.nreads;
+            rv.reset(new uint8_t[k + 1]); rl.reset(new uint8_t[k + 1]);
+            if (bfq_qs_rle_encode(ctx, qsl.get(), k, rv.get(), rl.get(), k, &nruns) != BFQ_OK) {
+                std::cerr << "Error: " << bfq_last_error() << endl; bfq_ctx_destroy(ctx); return EXIT_FAILURE;
+            }
+        }
         auto t2 = std::chrono::steady_clock::now();
         bfq_ctx_destroy(ctx);
 
@@ -178,6 +192,10 @@ int main(int argc, char **argv)
             const uint64_t k = (text_size - 6 * S.nreads) / 2 + S.nreads;
             bfqio::write_all(output + ".fq.dna", dna.get(), k);
             bfqio::write_all(output + ".fq.qs", qsl.get(), k);
+            if (rle) {
+                bfqio::write_all(output + ".fq.qs.rlv", rv.get(), nruns);
+                bfqio::write_all(output + ".fq.qs.rll", rl.get(), nruns);
+            }
         }
         auto t3 = std::chrono::steady_clock::now();
         std::cerr << "\nThe rebuilt file is ready!\n\n";
