@@ -331,8 +331,9 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
 // src (optional, only when radix_permutation_generates(n)): the first pass reads the smoothed rows instead of keys_a / vals_a.
 struct PermSource { const uint32_t *SA; const uint8_t *bwt, *qflat, *obase; uint32_t n_total; };
 bool radix_permutation_generates(uint64_t n);
+// verify: the keys come from outside the library (bfq_dist_place) -- check that they are a permutation of 0..n-1 (BFQ_EINVAL)
 int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n,
-                           const PermSource *src = nullptr);
+                           const PermSource *src = nullptr, bool verify = false);
 // Level-0 keys of the suffix sort: k symbols of every text position (cut at the terminator, QL[p] in the
 // unsorted bits 63..48 when given) with payload = position, built and histogrammed in one kernel, then sorted
 // on the 3k symbol bits.  Same result convention as radix_sort_pairs64.

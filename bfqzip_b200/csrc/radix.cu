@@ -723,14 +723,31 @@ static uint32_t count_digit(uint64_t n, int shift, int bits, uint32_t d)
 // bucket at smem[key & mask] and writes the bucket out in order.  No ranking, no key output: a pure stream.
 constexpr int PL_BITS = 15;
 constexpr int PL_THREADS = 512;
+// VERIFY (keys that come from outside: bfq_dist_place): every key must lie in this block's bucket and no slot may be
+// written twice -- then the keys of the bucket are exactly its positions; *bad is raised otherwise.
+template <bool VERIFY>
 __global__ void __launch_bounds__(PL_THREADS)
-rs_place_kernel(const uint32_t *__restrict__ keys, const uint16_t *__restrict__ vals, uint32_t n, uint16_t *__restrict__ out)
+rs_place_kernel(const uint32_t *__restrict__ keys, const uint16_t *__restrict__ vals, uint32_t n, uint16_t *__restrict__ out,
+                uint32_t *__restrict__ bad)
 {
     extern __shared__ __align__(16) uint16_t pl_smem[];
+    __shared__ uint32_t s_seen[VERIFY ? (1 << PL_BITS) / 32 : 1];
     const uint32_t base = blockIdx.x << PL_BITS;
     const uint32_t cnt = min(1u << PL_BITS, n - base);
-    for (uint32_t i = threadIdx.x; i < cnt; i += PL_THREADS)
-        pl_smem[__ldcs(keys + base + i) & ((1u << PL_BITS) - 1u)] = __ldcs(vals + base + i);
+    if constexpr (VERIFY) {
+        for (uint32_t i = threadIdx.x; i < (1u << PL_BITS) / 32; i += PL_THREADS) s_seen[i] = 0;
+        __syncthreads();
+    }
+    for (uint32_t i = threadIdx.x; i < cnt; i += PL_THREADS) {
+        const uint32_t k = __ldcs(keys + base + i), slot = k & ((1u << PL_BITS) - 1u);
+        if constexpr (VERIFY) {
+            if ((k >> PL_BITS) != blockIdx.x || slot >= cnt || (atomicOr(&s_seen[slot >> 5], 1u << (slot & 31)) >> (slot & 31)) & 1u) {
+                atomicOr(bad, 1u);
+                continue;
+            }
+        }
+        pl_smem[slot] = __ldcs(vals + base + i);
+    }
     __syncthreads();
     if (cnt == (1u << PL_BITS)) {
         const uint4 *s = reinterpret_cast<const uint4 *>(pl_smem);
@@ -741,13 +758,21 @@ rs_place_kernel(const uint32_t *__restrict__ keys, const uint16_t *__restrict__ 
     }
 }
 
+__global__ void __launch_bounds__(256)
+rs_key_range_kernel(const uint32_t *__restrict__ keys, uint32_t n, uint32_t *__restrict__ bad)
+{
+    bool b = false;
+    for (uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (uint64_t)gridDim.x * 256) b |= keys[i] >= n;
+    if (__any_sync(0xffffffffu, b) && (threadIdx.x & 31) == 0) atomicOr(bad, 2u);
+}
+
 bool radix_permutation_generates(uint64_t n)
 {
     return n > ((uint64_t)1 << PL_BITS) && n < ((uint64_t)1 << 32);      // at least one pass above the placement bits
 }
 
 int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint16_t *vals_a, uint16_t *vals_b, uint64_t n,
-                           const PermSource *src)
+                           const PermSource *src, bool verify)
 {
     if (src && !radix_permutation_generates(n)) BFQ_FAIL(BFQ_ECUDA, "internal error: no radix pass to generate the pairs in");
     if (n == 0) return 0;
@@ -760,6 +785,21 @@ int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint1
     for (int p = 0; p < P.num; p++) P.shift[p] += low;
     Arena::Mark mk = c->arena.mark();
     int flip = 0;
+    uint32_t *d_bad = nullptr;
+    if (verify) {
+        // the passes scatter with digit counts computed from n alone: a key >= n would be written out of bounds.  Checked
+        // before anything moves; duplicates (which stay inside the arrays) are caught by the placement kernel.
+        if (!low) BFQ_FAIL(BFQ_EINVAL, "pair lists must be 16-byte aligned");
+        d_bad = arena_alloc<uint32_t>(c, 4);
+        BFQ_CUDA(cudaMemsetAsync(d_bad, 0, 16, c->stream));
+        ProfScope ps(c, PC_UNPERMUTE, n * 4);
+        rs_key_range_kernel<<<(int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, 256)), 256, 0, c->stream>>>(keys_a, (uint32_t)n, d_bad);
+        BFQ_CUDA(cudaGetLastError());
+        fetch_small(c, c->h_small, d_bad, 4);
+        BFQ_CUDA(cudaStreamSynchronize(c->stream));
+        if (((const uint32_t *)c->h_small)[0])
+            BFQ_FAIL(BFQ_EINVAL, "the pair list holds a position outside [0, %llu): it is not the set of text positions of this rank", (unsigned long long)n);
+    }
     if (P.num) {
         uint32_t *hist = arena_alloc<uint32_t>(c, RS_MAX_PASSES * RS_RADIX);
         std::vector<uint32_t> h(RS_MAX_PASSES * RS_RADIX, 0);
@@ -771,12 +811,25 @@ int radix_sort_permutation(bfq_ctx *c, uint32_t *keys_a, uint32_t *keys_b, uint1
     }
     if (low) {
         const size_t smem = sizeof(uint16_t) << PL_BITS;
-        BFQ_CUDA(cudaFuncSetAttribute(rs_place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        BFQ_CUDA(cudaFuncSetAttribute(rs_place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        BFQ_CUDA(cudaFuncSetAttribute(rs_place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ProfScope ps(c, PC_UNPERMUTE, n * (4 + 2 + 2));
-        rs_place_kernel<<<div_up(n, (uint64_t)1 << PL_BITS), PL_THREADS, smem, c->stream>>>(
-            flip ? keys_b : keys_a, flip ? vals_b : vals_a, (uint32_t)n, flip ? vals_a : vals_b);
+        if (verify)
+            rs_place_kernel<true><<<div_up(n, (uint64_t)1 << PL_BITS), PL_THREADS, smem, c->stream>>>(
+                flip ? keys_b : keys_a, flip ? vals_b : vals_a, (uint32_t)n, flip ? vals_a : vals_b, d_bad);
+        else
+            rs_place_kernel<false><<<div_up(n, (uint64_t)1 << PL_BITS), PL_THREADS, smem, c->stream>>>(
+                flip ? keys_b : keys_a, flip ? vals_b : vals_a, (uint32_t)n, flip ? vals_a : vals_b, nullptr);
         BFQ_CUDA(cudaGetLastError());
         flip ^= 1;                                                  // only the values are in order now (the keys are known: 0..n-1)
+    }
+    if (verify) {
+        fetch_small(c, c->h_small, d_bad, 4);
+        BFQ_CUDA(cudaStreamSynchronize(c->stream));
+        if (((const uint32_t *)c->h_small)[0]) {
+            c->arena.release(mk);
+            BFQ_FAIL(BFQ_EINVAL, "the pair list is not a permutation of the rank's %llu text positions (a position is missing or doubled)", (unsigned long long)n);
+        }
     }
     c->arena.release(mk);
     return flip;

@@ -312,10 +312,19 @@ void place_pairs_dev(bfq_ctx *c, uint32_t *d_keys, uint16_t *d_vals, uint64_t cn
 {
     cudaStream_t st = c->stream;
     if (cnt == 0 || read_hi <= read_lo) return;
+    // the caller's numbers must describe one range of whole reads: cnt text positions from t_lo = off[read_lo] + read_lo on
+    fetch_small(c, c->h_small, d_off + read_lo, 8);
+    fetch_small(c, c->h_small + 1, d_off + read_hi, 8);
+    BFQ_CUDA(cudaStreamSynchronize(st));
+    if (c->h_small[0] + read_lo != t_lo || c->h_small[1] + read_hi - t_lo != cnt)
+        BFQ_FAIL(BFQ_EINVAL, "reads [%llu, %llu) cover text positions [%llu, %llu), not %llu positions from %llu on", (unsigned long long)read_lo,
+                 (unsigned long long)read_hi, (unsigned long long)(c->h_small[0] + read_lo), (unsigned long long)(c->h_small[1] + read_hi),
+                 (unsigned long long)cnt, (unsigned long long)t_lo);
+    if (cnt >= ((uint64_t)1 << 32)) BFQ_FAIL(BFQ_ETOOLARGE, "%llu positions for one rank; a rank indexes its positions with 32 bits", (unsigned long long)cnt);
     Arena::Mark mk = c->arena.mark();
     uint32_t *kb = arena_alloc<uint32_t>(c, cnt + 16);
     uint16_t *vb = arena_alloc<uint16_t>(c, cnt + 16);
-    const int flip = radix_sort_permutation(c, d_keys, kb, d_vals, vb, cnt);
+    const int flip = radix_sort_permutation(c, d_keys, kb, d_vals, vb, cnt, nullptr, /*verify=*/true);
     {
         const uint64_t nreads = read_hi - read_lo;
         ProfScope ps(c, PC_ASSEMBLE, cnt * 2 + (cnt - nreads) * 2);

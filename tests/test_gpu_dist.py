@@ -73,3 +73,41 @@ def test_dist_refuses_k_below_4():
             dist.emulate_ranks(eng, reads, lib.default_params(eos=0, K=3), 2)
     finally:
         eng.close()
+
+
+def test_dist_place_refuses_a_pair_list_that_is_not_a_permutation():
+    """bfq_dist_place is a public entry point: its keys come from an exchange outside the library.  A position outside the
+    rank's range, a doubled position or a range that does not match the reads must be refused (BFQ_EINVAL), not scattered."""
+    import torch
+    reads = synth.make_reads(3000, 80, 11)
+    off = np.ascontiguousarray(reads[2], np.uint64)
+    eng = dist.GpuEngine(2, 0, 0)
+    try:
+        nreads, total = len(off) - 1, int(off[-1])
+        tb = dist.text_bounds(off, [0, nreads])
+        dreads = eng.upload(reads)
+        sl = eng.build(0, 1, dreads, nreads, total, lib.default_params(eos=0), tb)
+        cnt = int(sl["counts"][0])
+        good_k, good_v = sl["keys"].clone(), sl["vals"].clone()
+        torch.cuda.synchronize()
+        ob, oq = eng.place(good_k.clone(), good_v.clone(), cnt, 0, dreads, 0, nreads, total)      # the intact list places
+        assert ob.numel() == total
+        for what in ("out_of_range", "doubled", "wrong_count", "wrong_start"):
+            k, v = good_k.clone(), good_v.clone()
+            args = dict(count=cnt, text_lo=0, read_lo=0, read_hi=nreads)
+            if what == "out_of_range":
+                k[cnt // 2] = cnt + 5
+            elif what == "doubled":
+                k[cnt // 3] = k[cnt // 3 + 1]
+            elif what == "wrong_count":
+                args["count"] = cnt - 16
+            else:
+                args["text_lo"] = 7
+            torch.cuda.synchronize()
+            with pytest.raises(lib.BfqError) as ei:
+                eng.place(k, v, args["count"], args["text_lo"], dreads, args["read_lo"], args["read_hi"], total)
+            assert ei.value.code == -3, what
+        ob2, oq2 = eng.place(good_k.clone(), good_v.clone(), cnt, 0, dreads, 0, nreads, total)     # and the context still works
+        assert torch.equal(ob, ob2) and torch.equal(oq, oq2)
+    finally:
+        eng.close()

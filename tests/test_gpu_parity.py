@@ -394,3 +394,21 @@ def test_part_a_tile_load_paths(bulk):
         c.set_option("bulk_tile", 1)
     assert np.array_equal(bwt, g["bwt"]) and np.array_equal(qs, g["qs"]) and np.array_equal(lcp, g["lcp"])
     assert np.array_equal(b2, rb) and np.array_equal(q2, rq) and np.array_equal(l2, rl)
+
+
+def test_two_base_cluster_list_overflow_is_retried():
+    """The list of two-frequent-base clusters (rule 11) is sized n / 8; a cluster needs only two rows, so valid input can
+    hold more.  The kernels count what they would have stored and the smoothing pass is repeated once with lists of that
+    size (r11_cap forces the overflow): same reads, same statistics as the oracle."""
+    g = np.load(os.path.join(H.GOLDEN, "syn_var_dup.npz"))
+    P = lib.default_params(eos=35, K=8, m=2)
+    c = ctx(3, 0)
+    c.set_option("r11_cap", 1)
+    try:
+        ob, oq, off, st = c.smooth_rebuild(g["bwt"], g["qs"], g["lcp"], P)
+    finally:
+        c.set_option("r11_cap", 0)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(g["bwt"], g["qs"], g["lcp"], H.make_params(M=3, B=0, K=8, m=2))
+    assert est["ambiguous"] + est["processed"] > 1            # the case really has more than one such cluster
+    assert np.array_equal(ob, eb) and np.array_equal(oq, eq) and np.array_equal(off, eoff)
+    assert all(st[k] == est[k] for k in STAT_KEYS)
