@@ -52,6 +52,19 @@ KNAME = {"radix_pass": "rs_onesweep_kernel", "radix_hist": "rs_hist_kernel", "pa
 BOUND = {"group": "issue", "walk": "dram-sector-rate", "rule11": "dram-sector-rate"}
 
 
+def workload_cfg2():
+    W = CFG2
+    return (f"BASELINE config 2: synthetic {W['nreads']} reads x {W['read_len']} bp single-end, M={W['M']} B={W['B']}, K=16 m=5 "
+            f"(seeded generator bfqzip_b200/synth.py make_reads, seed {W['seed']})")
+
+
+def workload_cfg4(npairs=None):
+    V = CFG4
+    npairs = npairs or V["npairs"]
+    return (f"BASELINE config 4: synthetic paired 2 x {npairs} reads x {V['read_len']} bp, M={V['M']} B={V['B']}, K=16 m=5, {V['blocks']} fixed blocks "
+            f"cut as split_fastq / split_fastq_2 do (counter-based generator bfqzip_b200/synth.py hash_paired, seed {V['seed']}, coverage {V['coverage']:g}, fragment {V['fragment']})")
+
+
 def measured_peak_gbs():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -241,7 +254,7 @@ def reference_arm(args):
     W = CFG2
     variants = {}
     if args.gpus <= 1:
-        workload = f"synthetic {W['nreads']} reads x {W['read_len']} bp single-end, M={W['M']} B={W['B']} (BASELINE config 2)"
+        workload = workload_cfg2()
         if have_ref():
             kind, used = "reference", cores
             n_full = W["nreads"] // (quick or 1)
@@ -268,8 +281,7 @@ def reference_arm(args):
         scaling = "weak"
     else:
         V = CFG4
-        workload = (f"synthetic paired 2 x {V['npairs']} reads x {V['read_len']} bp, M={V['M']} B={V['B']}, {V['blocks']} blocks "
-                    f"(BASELINE config 4; the reference side is BFQzip_parallel.py's concurrent block pipelines)")
+        workload = workload_cfg4()
         if not have_ref():
             _emit({"impl": "reference", "unavailable": "oracle/_ref is not built on this box; config 4 has no port leg"})
             return
@@ -287,7 +299,9 @@ def reference_arm(args):
     _emit({"impl": "reference", "metric": METRIC, "value": val, "unit": "Gbases/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "timed_runs": 1, "higher_is_better": True,
            "scaling": scaling, "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-           "config": {"workload": workload, "sample": sample}, "cpu_baseline": cpu,
+           # N = 1: the whole configuration is timed, the config equals the product arm's; N > 1: a stated sample of it
+           "config": ({"workload": workload} if args.gpus <= 1 and kind == "reference" and not quick else {"workload": workload, "sample": sample}),
+           "cpu_baseline": cpu,
            "e2e": {"value": val, "unit": "Gbases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0})
 
 
@@ -429,8 +443,7 @@ def bench_cfg2(env, steps, warmup):
     return dict(ms=ms, ms_e2e=ms_e2e, steps=steps, bases_per_step=total * env.world, launches=int(launches), prof=prof, stats=res["st"],
                 clocks=sampler.summary(), rows_per_gpu=N, h2d=int(2 * total + 8 * (nreads + 1)) * env.world,
                 d2h=int(3 * N + 2 * total) * env.world, e2e_equals_device=same,
-                workload=(f"synthetic {W['nreads']} reads x {W['read_len']} bp single-end per GPU, M={M} B={B}, K=16 m=5 eos=0 "
-                          f"(BASELINE config 2; seeded generator bfqzip_b200/synth.py make_reads, seed {W['seed']}+rank)"))
+                workload=workload_cfg2() + (f"; one such collection per GPU, seed {W['seed']}+rank" if env.world > 1 else ""))
 
 
 def bench_cfg4(env, steps, warmup):
@@ -519,9 +532,7 @@ def bench_cfg4(env, steps, warmup):
                 stats={key: int(v) for key, v in zip(keys, summed)}, checks_ok=summed[-2] == env.world, e2e_equals_device=summed[-1] == env.world,
                 clocks=sampler.summary(), rows_per_gpu=sum(k["N"] for k in blocks), blocks_per_gpu=len(blocks),
                 h2d=int(2 * total_all + 8 * (2 * npairs + V["blocks"])), d2h=int(3 * N_all + 2 * total_all),
-                workload=(f"synthetic paired 2 x {npairs} reads x {L} bp, M={M} B={B}, K=16 m=5 eos=0, {V['blocks']} fixed blocks of {2 * (cuts[0][1] - cuts[0][0])} reads "
-                          f"cut as split_fastq/split_fastq_2 do (BASELINE config 4; counter-based generator bfqzip_b200/synth.py hash_paired, seed {V['seed']}, "
-                          f"genome {glen} bp, fragment {V['fragment']}; each block generated on the GPU that processes it)"))
+                workload=workload_cfg4(npairs))
 
 
 def bench_single(env, steps, warmup):
