@@ -401,13 +401,20 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
     __shared__ uint32_t s_stats[ST_COUNT];
     __shared__ uint8_t s_lut[256];
 #if BFQ_M == 1
-    __shared__ __align__(16) uint8_t s_code[CL_S], s_q[CL_S];
+    // M=1 adds the error probabilities of a cluster serially, in row order (double addition is not associative).  Per row
+    // that loop reads ONE index byte -- the quality, or 128 for an end-marker row -- and one table entry from shared memory
+    // (entry 128 = +0.0, whose addition is exact); the table in constant memory would serialise its divergent lookups.
+    __shared__ __align__(16) uint8_t s_qi[CL_S];
+    __shared__ double s_err[129];
 #endif
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
     const int64_t t0 = (int64_t)blockIdx.x * CL_TILE;
     const int64_t nn = (int64_t)n;
     for (int i = tid; i < 256; i += CLT_THREADS) s_lut[i] = g_sc.byte2code[i];
     if (tid < ST_COUNT) s_stats[tid] = 0;
+#if BFQ_M == 1
+    for (int i = tid; i < 129; i += CLT_THREADS) s_err[i] = i < 128 ? g_errtab[i] : 0.0;
+#endif
     __syncthreads();
 
     // ---- 1. this thread's 16 rows
@@ -471,8 +478,15 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
         s_fb[CL_CHUNKS] = f ? 1u : 0u;
     }
 #if BFQ_M == 1
-    *reinterpret_cast<uint4 *>(s_code + r0) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
-    *reinterpret_cast<uint4 *>(s_q + r0) = make_uint4(qw[0], qw[1], qw[2], qw[3]);
+    {
+        uint32_t qi[4];
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+            const uint32_t nz = (((cw[w] + 0x7F7F7F7Fu) & 0x80808080u) >> 7) * 0xFFu;       // 0xFF where the code is not the end-marker (codes are <= 5)
+            qi[w] = (qw[w] & 0x7F7F7F7Fu & nz) | (0x80808080u & ~nz);
+        }
+        *reinterpret_cast<uint4 *>(s_qi + r0) = make_uint4(qi[0], qi[1], qi[2], qi[3]);
+    }
 #endif
     // bit planes of the 16 codes and the "quality >= qthr + 33" bits (qualities are < 128: smooth_dev checks)
     uint32_t p0 = 0, p1 = 0, p2 = 0, hq = 0;
@@ -599,7 +613,7 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
                     A.base_num = A.freq[1] + A.freq[2] + A.freq[3] + A.freq[4] + A.freq[5];
                     A.mx = acc[4]; A.isum = (int32_t)acc[4]; A.dsum = 0.0;
 #if BFQ_M == 1
-                    for (int r = a; r < e; r++) if (s_code[r]) A.dsum = __dadd_rn(A.dsum, g_errtab[s_q[r]]);
+                    for (int r = a; r < e; r++) A.dsum = __dadd_rn(A.dsum, s_err[s_qi[r]]);
 #endif
                     const Decision d = decide(g_sc, len, A, st);
                     if (d.act == ACT_RULE11) {
