@@ -670,8 +670,10 @@ cluster_tile_kernel(SC_ARG, const uint8_t *__restrict__ bwt, const uint8_t *__re
 #pragma unroll
                 for (int w = 0; w < 4; w++) {
                     const uint32_t q = qw[w];
-                    // rows of the min set whose quality is above the new one (both are below 128: bit 7 of the difference)
-                    const uint32_t lt = ~((nq[w] | 0x80808080u) - q) & 0x80808080u & expand4(MINC >> (4 * w));
+                    // rows of the min set whose quality is above the new one (both are below 128: bit 7 of the difference).
+                    // Bit 7 of q is masked out: a row that an EARLIER round of this loop marked as replaced carries it, and
+                    // its borrow would flip the compare of the next byte when that row's quality equals the new one.
+                    const uint32_t lt = ~((nq[w] | 0x80808080u) - (q & 0x7F7F7F7Fu)) & 0x80808080u & expand4(MINC >> (4 * w));
                     st[ST_SMOOTHED] += __popc(lt);
                     const uint32_t take = expand4(EQ >> (4 * w)) | ((lt >> 7) * 0xFFu);
                     qw[w] = (q & ~take) | (nq[w] & take) | (expand4(MOD >> (4 * w)) & 0x80808080u);

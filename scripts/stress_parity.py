@@ -34,21 +34,25 @@ def main():
         nreads = int(rng.integers(2000, 9000))
         err = float(rng.choice([0.0, 0.01, 0.05]))
         var_len = bool(rng.integers(0, 2))
-        opts = {"batch_min_groups": int(rng.choice([0, 64, 1 << 20])), "rebuild": int(rng.choice([0, 1, 2]))}
+        opts = {"batch_min_groups": int(rng.choice([0, 64, 1 << 20])), "rebuild": int(rng.choice([0, 1, 2])),
+                "long_cluster": int(rng.choice([4, 16, 64, 1024])), "bulk_tile": int(rng.integers(0, 2))}
+        # the cluster parameters of bfq_ext (-k -m -t -f -v); f >= 34 keeps at most two frequent symbols (the reference asserts otherwise)
+        K, m = int(rng.choice([1, 2, 4, 8, 16, 16, 30])), int(rng.choice([2, 3, 5, 5, 8]))
+        qthr, fthr, dq = int(rng.choice([10, 20, 20, 35])), float(rng.choice([34, 40, 40, 50, 60])), int(rng.choice([62, 35, 73]))
         bases, quals, off = synth.make_reads(nreads, L, 1000 + case, coverage=cov, err=err, var_len=var_len)
         if (M, B) not in ctxs:
             ctxs[(M, B)] = lib.BfqGpu(M, B, 0)
         g = ctxs[(M, B)]
         for k, v in opts.items():
             g.set_option(k, v)
-        P = lib.default_params(eos=35)
+        P = lib.default_params(eos=35, K=K, m=m, qthr=qthr, fthr=fthr, default_q=dq)
         (bwt, qs, lcp), (ob, oq), st = g.pipeline(bases, quals, off, P)
         rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
         ok_a = np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
-        eb, eq, eoff, est, _, _, e = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B))
+        eb, eq, eoff, est, _, _, e = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B, K=K, m=m, qthr=qthr, fthr=fthr, default_q=dq))
         ok_c = e == 0 and np.array_equal(ob, eb) and np.array_equal(oq, eq) and all(
             st[k] == est[k] for k in ("clusters", "discarded", "ambiguous", "processed", "bases_inside", "qs_smoothed", "modified"))
-        print(f"case {case}: M={M} B={B} cov={cov} L={L} reads={nreads} err={err} var_len={var_len} {opts} "
+        print(f"case {case}: M={M} B={B} K={K} m={m} t={qthr} f={fthr} v={dq} cov={cov} L={L} reads={nreads} err={err} var_len={var_len} {opts} "
               f"partA={'ok' if ok_a else 'DIFF'} partBC={'ok' if ok_c else 'DIFF'}", flush=True)
         bad += (not ok_a) + (not ok_c)
     print("stress_parity:", "all ok" if bad == 0 else f"{bad} differences")

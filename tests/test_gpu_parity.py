@@ -412,3 +412,17 @@ def test_two_base_cluster_list_overflow_is_retried():
     assert est["ambiguous"] + est["processed"] > 1            # the case really has more than one such cluster
     assert np.array_equal(ob, eb) and np.array_equal(oq, eq) and np.array_equal(off, eoff)
     assert all(st[k] == est[k] for k in STAT_KEYS)
+
+
+@pytest.mark.parametrize("M", [1, 3])
+def test_more_than_1024_clusters_per_tile(M):
+    """-k 4 -m 3 at 2x coverage leaves ~1470 tiny clusters in every 4608-row window of cluster_tile_kernel: more than its
+    1024 accumulators, so it works in rounds.  (Found by scripts/stress_parity.py: a row marked as replaced in one round
+    made the packed quality compare of the next round count a neighbouring row as smoothed once too often.)"""
+    bases, quals, off = synth.make_reads(3707, 250, 1123, coverage=2.0, err=0.05)
+    rb, rq, rl = H.oracle_build_ebwt(bases, quals, off, 35)
+    P = lib.default_params(eos=35, K=4, m=3, qthr=10, fthr=40.0, default_q=73)
+    ob, oq, o2, st = ctx(M, 0).smooth_rebuild(rb, rq, rl, P)
+    eb, eq, eoff, est, _, _, err = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=0, K=4, m=3, qthr=10, fthr=40.0, default_q=73))
+    assert np.array_equal(ob, eb) and np.array_equal(oq, eq) and np.array_equal(o2, eoff)
+    assert {k: st[k] for k in STAT_KEYS} == {k: est[k] for k in STAT_KEYS}
