@@ -16,11 +16,46 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np  # noqa: E402
 
 
+def dist_sweep(a):
+    """Single-collection mode (bfq_dist_build / bfq_dist_place): W emulated ranks on one GPU against the oracle on the whole collection."""
+    import helpers as H
+    from bfqzip_b200 import dist, lib, synth
+    rng = np.random.default_rng(a.seed)
+    bad = 0
+    for case in range(a.cases):
+        M, B = int(rng.integers(0, 4)), int(rng.integers(0, 2))
+        W = int(rng.choice([1, 2, 3, 4, 5, 8]))
+        cov = float(rng.choice([3, 8, 40, 70])); L = int(rng.choice([30, 75, 100, 150, 250]))
+        nreads = int(rng.integers(1500, 7000)); err = float(rng.choice([0.0, 0.01, 0.05])); var_len = bool(rng.integers(0, 2))
+        K, m = int(rng.choice([4, 8, 16, 16, 30])), int(rng.choice([2, 3, 5, 5, 8]))          # the mode needs -k >= 4
+        qthr, fthr = int(rng.choice([10, 20, 20, 35])), float(rng.choice([34, 40, 40, 50, 60]))
+        opts = {"wide_positions": int(rng.integers(0, 2)), "group_cap": int(rng.choice([8, 1 << 20])), "bulk_tile": int(rng.integers(0, 2))}
+        reads = synth.make_reads(nreads, L, 5000 + case, coverage=cov, err=err, var_len=var_len)
+        eng = dist.GpuEngine(M, B, 0, opts)
+        try:
+            bwt, qs, lcp, ob, oq, st = dist.emulate_ranks(eng, reads, lib.default_params(eos=0, K=K, m=m, qthr=qthr, fthr=fthr), W)
+        finally:
+            eng.close()
+        rb, rq, rl = H.oracle_build_ebwt(*reads, 0)
+        ok_a = np.array_equal(bwt, rb) and np.array_equal(qs, rq) and np.array_equal(lcp, rl)
+        eb, eq, eoff, est, _, _, e = H.oracle_smooth_rebuild(rb, rq, rl, H.make_params(M=M, B=B, K=K, m=m, qthr=qthr, fthr=fthr, eos=0))
+        ok_c = e == 0 and np.array_equal(ob, eb) and np.array_equal(oq, eq) and all(
+            st[k] == est[k] for k in ("clusters", "discarded", "ambiguous", "processed", "bases_inside", "qs_smoothed", "modified"))
+        print(f"dist case {case}: W={W} M={M} B={B} K={K} m={m} t={qthr} f={fthr} cov={cov} L={L} reads={nreads} err={err} var_len={var_len} {opts} "
+              f"partA={'ok' if ok_a else 'DIFF'} partBC={'ok' if ok_c else 'DIFF'}", flush=True)
+        bad += (not ok_a) + (not ok_c)
+    print("stress_parity --dist:", "all ok" if bad == 0 else f"{bad} differences")
+    sys.exit(1 if bad else 0)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", type=int, default=24)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--dist", action="store_true", help="the single-collection mode instead: dist.emulate_ranks with a random number of ranks")
     a = ap.parse_args()
+    if a.dist:
+        return dist_sweep(a)
     import helpers as H
     from bfqzip_b200 import lib, synth
 
