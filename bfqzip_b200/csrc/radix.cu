@@ -471,22 +471,25 @@ static int radix_sort_pairs(bfq_ctx *c, K *keys_a, K *keys_b, V *vals_a, V *vals
 // Single-collection mode over several GPUs: every rank holds the whole packed text and sorts only the suffixes
 // whose key lies in its range.  The ranges are cut on the first four symbols (top 12 of the 48 key bits) from a
 // histogram every rank computes identically, so no splitter exchange is needed and equal keys never straddle ranks.
-__device__ __forceinline__ uint64_t suffix_key(const uint64_t *__restrict__ T3, uint64_t p, int k)
-{
-    uint64_t w = text_window(T3, p);
-    const int f = leading_nonzero_fields(w);          // symbols before the first terminator
-    if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
-    return w >> (64 - 3 * k);
-}
-
-// the same key for a window that starts `s` bits (s < 128) into three consecutive words of the packed text: consecutive
-// positions share the words, so a thread that takes a run of positions loads them once
-__device__ __forceinline__ uint64_t suffix_key3(uint64_t w0, uint64_t w1, uint64_t w2, int s, int k)
+// the 21-symbol window that starts `s` bits (s < 128) into three consecutive words
+__device__ __forceinline__ uint64_t window3(uint64_t w0, uint64_t w1, uint64_t w2, int s)
 {
     uint64_t w;
     if (s < 64) w = s ? ((w0 << s) | (w1 >> (64 - s))) : w0;
     else { const int t = s - 64; w = t ? ((w1 << t) | (w2 >> (64 - t))) : w1; }
-    w &= ~1ull;
+    return w & ~1ull;
+}
+// its first four symbols, cut at the terminator: the top RS_TOP_BITS bits of the suffix key, which is all the range test needs
+__device__ __forceinline__ uint32_t window_top12(uint64_t w)
+{
+    const uint32_t t = (uint32_t)(w >> 52);
+    if (!(t & 0xE00u)) return 0u;
+    if (!(t & 0x1C0u)) return t & 0xE00u;
+    if (!(t & 0x038u)) return t & 0xFC0u;
+    return t;
+}
+__device__ __forceinline__ uint64_t window_key(uint64_t w, int k)
+{
     const int f = leading_nonzero_fields(w);          // symbols before the first terminator
     if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
     return w >> (64 - 3 * k);
@@ -510,7 +513,7 @@ rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint64_t n, int k, uint32_t 
         const uint64_t w0 = T3[wi], w1 = T3[wi + 1], w2 = T3[wi + 2];      // 16 windows: 3 * 15 + 63 + s0 < 192 bits
 #pragma unroll
         for (int i = 0; i < RS_SEL_ITEMS; i++)
-            if (p0 + i < n) atomicAdd(&sh[(uint32_t)(suffix_key3(w0, w1, w2, s0 + 3 * i, k) >> (3 * k - RS_TOP_BITS))], 1u);
+            if (p0 + i < n) atomicAdd(&sh[window_top12(window3(w0, w1, w2, s0 + 3 * i))], 1u);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < (1 << RS_TOP_BITS); i += RS_THREADS)
@@ -521,8 +524,8 @@ rs_top_hist_kernel(const uint64_t *__restrict__ T3, uint64_t n, int k, uint32_t 
 // WRITE = true : ordered compaction (position order is kept: the sort relies on it for ties) + digit histograms
 template <bool WRITE, typename V>
 __global__ void __launch_bounds__(RS_THREADS)
-rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint64_t n, int k, uint64_t lo,
-                 uint64_t hi, RsPasses P, uint32_t *__restrict__ chunk_count, const uint32_t *__restrict__ chunk_base,
+rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint64_t n, int k, uint32_t b0,
+                 uint32_t b1, int pb, RsPasses P, uint32_t *__restrict__ chunk_count, const uint32_t *__restrict__ chunk_base,
                  unsigned long long *__restrict__ prev_key, uint64_t *__restrict__ keys, V *__restrict__ vals,
                  uint32_t *__restrict__ hist)
 {
@@ -542,9 +545,13 @@ rs_select_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ Q
         const uint64_t p = p0 + i;
         key[i] = ~0ull;
         if (p < n) {
-            const uint64_t kk = suffix_key3(w0, w1, w2, s0 + 3 * i, k);
-            if (kk >= lo && kk < hi) { key[i] = kk; mine++; }
-            else if (!WRITE && kk < lo) { below = max(below, (unsigned long long)kk); any_below = true; }
+            // The ranges are cut on the first four symbols, so those decide membership; the full key is built only for the
+            // positions of this rank (1 / world of them) and, in the counting pass, for the positions of the last non-empty
+            // bin below the range (pb, known from the histogram): the largest key below the range lies there.
+            const uint64_t w = window3(w0, w1, w2, s0 + 3 * i);
+            const uint32_t t = window_top12(w);
+            if (t >= b0 && t < b1) { key[i] = window_key(w, k); mine++; }
+            else if (!WRITE && (int)t == pb) { below = max(below, (unsigned long long)window_key(w, k)); any_below = true; }
         }
     }
     uint32_t x = mine;
@@ -653,11 +660,11 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
     // (the 32-bit bin counters wrap for a bin of 2^32 suffixes; such a collection fails the capacity check below)
     if (mine >= ((uint64_t)1 << 32) - 64)
         BFQ_FAIL(BFQ_ETOOLARGE, "rank %d of %d would sort %llu suffixes; one GPU indexes its rows with 32 bits", rank, world, (unsigned long long)mine);
-    const int sh = 3 * k - RS_TOP_BITS;
-    const uint64_t lo = (uint64_t)b0 << sh, hi = (uint64_t)b1 << sh;
+    int pb = -1;                                           // last non-empty bin below the range: it holds the key before the rank's first row
+    for (uint32_t b = 0; b < b0; b++) if (h[b]) pb = (int)b;
     {
         ProfScope ps(c, PC_KEYS, n * 3 / 8, 2);
-        rs_select_kernel<false, V><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, n, k, lo, hi, P, cc, nullptr, d_prev, nullptr, nullptr, nullptr);
+        rs_select_kernel<false, V><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, n, k, b0, b1, pb, P, cc, nullptr, d_prev, nullptr, nullptr, nullptr);
         rs_scan_chunks_kernel<<<1, 1024, 0, st>>>(cc, cb, nchunks, (uint32_t *)(d_prev + 1));
         BFQ_CUDA(cudaGetLastError());
     }
@@ -674,7 +681,7 @@ int radix_sort_suffix_keys_range(bfq_ctx *c, const uint64_t *T3, const uint16_t 
     if (cnt) {
         {
             ProfScope ps(c, PC_KEYS, n * 3 / 8 + cnt * 14);
-            rs_select_kernel<true, V><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, n, k, lo, hi, P, nullptr, cb, nullptr, keys_a, pos_a, hist);
+            rs_select_kernel<true, V><<<nchunks, RS_THREADS, 0, st>>>(T3, QL, n, k, b0, b1, pb, P, nullptr, cb, nullptr, keys_a, pos_a, hist);
             BFQ_CUDA(cudaGetLastError());
         }
         flip = radix_passes<uint64_t, V, 16>(c, keys_a, keys_b, pos_a, pos_b, cnt, P, hist);
