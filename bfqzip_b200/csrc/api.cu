@@ -134,7 +134,17 @@ static void pipeline_dev(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d_qu
         c->trace("files on host (copy stream)", c->copy_stream);
     }
     SmoothResult S;
-    smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats, d_sa, d_t3);
+    {
+        // what part A knows about its own outputs: bwt = the reads' bases + one end-marker per read; qs = their qualities + the
+        // end-marker byte at the same rows (main.c:848-867).  Saves two passes over 2 N bytes and two synchronisations.
+        uint64_t bh[256], qh[256];
+        const bool known = c->has_qual_hist;
+        if (known) {
+            memcpy(bh, c->base_hist, sizeof bh); memcpy(qh, c->qual_hist, sizeof qh);
+            bh[P->eos_byte] += nreads; qh[P->eos_byte] += nreads;
+        }
+        smooth_dev(c, d_bwt, d_qs, d_lcp, N, P, &S, stats, d_sa, d_t3, nullptr, false, known ? bh : nullptr, known ? qh : nullptr);
+    }
     c->trace("part B done", c->stream);
     if (S.nreads != nreads) BFQ_FAIL(BFQ_ECUDA, "internal error: %llu end-markers for %llu reads", (unsigned long long)S.nreads, (unsigned long long)nreads);
     if (flat) unpermute_dev(c, S, d_bwt, d_sa, d_off, nreads, d_out_bases, d_out_quals);

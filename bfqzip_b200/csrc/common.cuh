@@ -200,6 +200,8 @@ struct bfq_ctx {
     const uint8_t *last_flat_bwt = nullptr; // flat mode: the BWT bytes the stored qualities belong to
     uint64_t last_n = 0;
     uint64_t base_hist[256] = {0};   // byte histogram of the reads of the last part-A call
+    uint64_t qual_hist[256] = {0};   // ... and of their qualities (has_qual_hist), so that the fused pipeline does not histogram bwt / qs again
+    bool has_qual_hist = false;
     uint8_t last_code2byte[8] = {0};
     bfq::Arena::Mark last_mark{0, 0};
     bool has_last = false;
@@ -296,7 +298,10 @@ struct SmoothResult {
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
                 uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
                 const void *d_sa = nullptr, const uint64_t *d_t3 = nullptr, const uint64_t *alpha_hist = nullptr,
-                bool sa_wide = false);      // sa_wide: d_sa holds u64 positions (else u32)
+                bool sa_wide = false,       // sa_wide: d_sa holds u64 positions (else u32)
+                const uint64_t *known_bwt_hist = nullptr, const uint64_t *known_qs_hist = nullptr);
+// known_*_hist (fused pipeline): the byte histograms of d_bwt and d_qs, which part A knows -- the BWT holds the reads' bases plus one
+// end-marker per read, the permuted qualities are the reads' qualities plus one end-marker byte per read -- so they are not recomputed.
 // alpha_hist: byte histogram that fixes the alphabet (single-collection mode: the rows are a slice of the global eBWT
 // and may miss a symbol); NULL = histogram of d_bwt itself, as buildFreq does.
 // rebuild.cu

@@ -922,7 +922,8 @@ static void launch_check(bfq_ctx *c) { BFQ_CUDA(cudaGetLastError()); (void)c; }
 
 void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uint8_t *d_lcp,
                 uint64_t n, const bfq_params *P, SmoothResult *out, bfq_stats *stats,
-                const void *d_sa, const uint64_t *d_t3, const uint64_t *alpha_hist, bool sa_wide)
+                const void *d_sa, const uint64_t *d_t3, const uint64_t *alpha_hist, bool sa_wide,
+                const uint64_t *known_bwt_hist, const uint64_t *known_qs_hist)
 {
     const bool flat = d_sa != nullptr && d_t3 != nullptr;
     out->flat = flat;
@@ -933,8 +934,8 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
 
     // ---- buildFreq (bfq_ext.cpp:132-187): symbol counts, alphabet in byte order, pile starts
     uint64_t hist[256], qhist[256];
-    byte_histogram(c, d_bwt, n, hist);
-    byte_histogram(c, d_qs, n, qhist);
+    if (known_bwt_hist && known_qs_hist) { memcpy(hist, known_bwt_hist, sizeof hist); memcpy(qhist, known_qs_hist, sizeof qhist); }
+    else { byte_histogram(c, d_bwt, n, hist); byte_histogram(c, d_qs, n, qhist); }
     for (int b = 128; b < 256; b++)
         if (qhist[b]) BFQ_FAIL(BFQ_EINVAL, "quality byte %d >= 128 is not a FASTQ quality", b);
     Alphabet A = alphabet_from_hist(alpha_hist ? alpha_hist : hist, P->eos_byte, /*eos_may_appear=*/true);
@@ -963,15 +964,15 @@ void smooth_dev(bfq_ctx *c, const uint8_t *d_bwt, const uint8_t *d_qs, const uin
     }
 #endif
     uint32_t *d_pile = (uint32_t *)((char *)c->d_small + 2048);
-    {
+    if (!flat) {                          // (flat mode builds no walk lines: the pile starts are not needed)
         uint32_t pile[8] = {0};
         uint64_t acc = hist[P->eos_byte];
         for (int k = 1; k <= 5; k++) { pile[k - 1] = (uint32_t)acc; if (k <= A.nsym) acc += hist[A.code2byte[k]]; }
         uint32_t *h = (uint32_t *)((char *)c->h_small + 2048);
         memcpy(h, pile, sizeof pile);
         BFQ_CUDA(cudaMemcpyAsync(d_pile, h, sizeof pile, cudaMemcpyHostToDevice, st));
+        BFQ_CUDA(cudaStreamSynchronize(st));     // the pinned staging above is reused by later calls
     }
-    BFQ_CUDA(cudaStreamSynchronize(st));     // the pageable/pinned staging above is reused by later calls
 
     // ---- walk lines (computeVectorUnbuildBCR, decode.cpp:87-235, + tableOcc)
     static_assert(RK_ROWS == (1 << WS_SUPER_SHIFT), "a rank block is one super-block of the walk sectors");

@@ -48,6 +48,22 @@ hist256_kernel(const uint8_t *__restrict__ data, uint64_t n, unsigned long long 
     if (sh[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
 }
 
+// two arrays under one synchronisation (the reads' bases and qualities in part A)
+void byte_histogram2(bfq_ctx *c, const uint8_t *d_a, const uint8_t *d_b, uint64_t n, uint64_t hist_a[256], uint64_t hist_b[256])
+{
+    unsigned long long *d_hist = (unsigned long long *)c->d_small;   // the whole 4 KiB block: 2 x 256 x 8 bytes
+    BFQ_CUDA(cudaMemsetAsync(d_hist, 0, 2 * 256 * 8, c->stream));
+    if (n) {
+        ProfScope ps(c, PC_HIST, 2 * n, 2);
+        int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, 256 * 16) + 1);
+        hist256_kernel<<<grid, 256, 0, c->stream>>>(d_a, n, d_hist);
+        hist256_kernel<<<grid, 256, 0, c->stream>>>(d_b, n, d_hist + 256);
+    }
+    fetch_small(c, c->h_small, d_hist, 2 * 256 * 8);
+    BFQ_CUDA(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 256; i++) { hist_a[i] = c->h_small[i]; hist_b[i] = c->h_small[256 + i]; }
+}
+
 void byte_histogram(bfq_ctx *c, const uint8_t *d_data, uint64_t n, uint64_t hist_out[256])
 {
     unsigned long long *d_hist = (unsigned long long *)c->d_small;   // 256*8 = 2 KiB of the 4 KiB
@@ -965,8 +981,9 @@ static void build_ebwt_impl(bfq_ctx *c, const uint8_t *d_bases, const uint8_t *d
 
     // ---- alphabet from the data (codes follow byte order, like gsufsort's +1 remap)
     uint64_t hist[256];
-    byte_histogram(c, d_bases, total_bases, hist);
-    c->trace("part A: byte histogram", st);
+    if (d_quals && d_quals != d_bases) { byte_histogram2(c, d_bases, d_quals, total_bases, hist, c->qual_hist); c->has_qual_hist = true; }
+    else { byte_histogram(c, d_bases, total_bases, hist); c->has_qual_hist = false; }
+    c->trace("part A: byte histograms", st);
     memcpy(c->base_hist, hist, sizeof hist);
     Alphabet A = alphabet_from_hist(hist, eos, /*eos_may_appear=*/false);
     // gsufsort drops bytes <= 1 and 255 (utils.c:229-236); refuse them instead of silently differing
