@@ -52,6 +52,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", type=int, default=24)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--big", action="store_true", help="30 000 - 120 000 reads per case instead of 2 000 - 9 000 (the oracle needs up to a minute per case)")
     ap.add_argument("--dist", action="store_true", help="the single-collection mode instead: dist.emulate_ranks with a random number of ranks")
     a = ap.parse_args()
     if a.dist:
@@ -66,7 +67,7 @@ def main():
         M, B = int(rng.integers(0, 4)), int(rng.integers(0, 2))
         cov = float(rng.choice([2, 3, 5, 8, 15, 40, 70]))
         L = int(rng.choice([30, 75, 100, 150, 250]))
-        nreads = int(rng.integers(2000, 9000))
+        nreads = int(rng.integers(30000, 120000)) if a.big else int(rng.integers(2000, 9000))
         err = float(rng.choice([0.0, 0.01, 0.05]))
         var_len = bool(rng.integers(0, 2))
         opts = {"batch_min_groups": int(rng.choice([0, 64, 1 << 20])), "rebuild": int(rng.choice([0, 1, 2])),
