@@ -220,12 +220,13 @@ extern "C" {
 
 int bfq_qs_rle_encode(bfq_ctx *ctx, const uint8_t *qs, uint64_t n, uint8_t *vals, uint8_t *lens, uint64_t capacity, uint64_t *nruns)
 {
+    Arena::Mark mk{0, 0}; bool marked = false;            // scratch is released on the error path too
     try {
         if (!ctx || !nruns || (n && (!qs || !vals || !lens))) BFQ_FAIL(BFQ_EINVAL, "bfq_qs_rle_encode: null pointer");
         *nruns = 0;
         BFQ_CUDA(cudaSetDevice(ctx->device));
         if (n == 0) return BFQ_OK;
-        Arena::Mark mk = ctx->arena.mark();
+        mk = ctx->arena.mark(); marked = true;
         uint8_t *d_q = arena_alloc<uint8_t>(ctx, n + 64);
         const uint64_t cap = std::min<uint64_t>(capacity, n);
         uint8_t *d_v = arena_alloc<uint8_t>(ctx, cap + 64), *d_l = arena_alloc<uint8_t>(ctx, cap + 64);
@@ -237,17 +238,18 @@ int bfq_qs_rle_encode(bfq_ctx *ctx, const uint8_t *qs, uint64_t n, uint8_t *vals
         ctx->arena.release(mk);
         *nruns = r;
         return BFQ_OK;
-    } catch (bfq::Error &e) { if (ctx) { cudaStreamSynchronize(ctx->stream); } cudaGetLastError(); return e.code; }
+    } catch (bfq::Error &e) { if (ctx) { cudaStreamSynchronize(ctx->stream); if (marked) ctx->arena.release(mk); } cudaGetLastError(); return e.code; }
 }
 
 int bfq_qs_rle_decode(bfq_ctx *ctx, const uint8_t *vals, const uint8_t *lens, uint64_t nruns, uint8_t *qs, uint64_t capacity, uint64_t *n)
 {
+    Arena::Mark mk{0, 0}; bool marked = false;
     try {
         if (!ctx || !n || (nruns && (!vals || !lens || !qs))) BFQ_FAIL(BFQ_EINVAL, "bfq_qs_rle_decode: null pointer");
         *n = 0;
         BFQ_CUDA(cudaSetDevice(ctx->device));
         if (nruns == 0) return BFQ_OK;
-        Arena::Mark mk = ctx->arena.mark();
+        mk = ctx->arena.mark(); marked = true;
         uint8_t *d_v = arena_alloc<uint8_t>(ctx, nruns + 64), *d_l = arena_alloc<uint8_t>(ctx, nruns + 64);
         uint8_t *d_o = arena_alloc<uint8_t>(ctx, capacity + 64);
         BFQ_CUDA(cudaMemcpyAsync(d_v, vals, nruns, cudaMemcpyHostToDevice, ctx->stream));
@@ -258,7 +260,7 @@ int bfq_qs_rle_decode(bfq_ctx *ctx, const uint8_t *vals, const uint8_t *lens, ui
         ctx->arena.release(mk);
         *n = len;
         return BFQ_OK;
-    } catch (bfq::Error &e) { if (ctx) { cudaStreamSynchronize(ctx->stream); } cudaGetLastError(); return e.code; }
+    } catch (bfq::Error &e) { if (ctx) { cudaStreamSynchronize(ctx->stream); if (marked) ctx->arena.release(mk); } cudaGetLastError(); return e.code; }
 }
 
 } // extern "C"
