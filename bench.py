@@ -590,9 +590,9 @@ def bench_single(env, steps, warmup):
 
 
 # ncu dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant classes, config 2, device-resident step
-# (profiles/r2_hot_kernels.txt, one `ncu --set full` capture of round 2): the `traffic` figure of the roofline object
-TRAFFIC_CFG2 = {"group": 1940.1e6, "radix_pass": 2404.6e6, "cluster": 419.7e6, "keys": 1396.1e6, "pack": 284.6e6,
-                "assemble": 367.9e6, "unpermute": 1076.6e6}      # pack / unpermute: mean over the class's launches
+# (profiles/r2z_hot_kernels.txt, the `ncu --set full` capture of the final round-2 code): the `traffic` figure of the roofline object
+TRAFFIC_CFG2 = {"group": 1938.9e6, "radix_pass": 2404.1e6, "cluster": 421.4e6, "keys": 1393.4e6, "pack": 284.3e6,
+                "assemble": 366.0e6, "unpermute": 1079.7e6}      # pack / unpermute: mean over the class's launches
 
 
 def headline(r, env, args, scaling, traffic):
