@@ -120,6 +120,17 @@ __device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
     return lz / 3;
 }
 
+// the window with every symbol after its first terminator cleared (what `f = leading_nonzero_fields(w); if (f < 21)
+// w &= f ? ~0ull << (64 - 3 * f) : 0` computes, without the division: the count of leading zeros IS 3 f)
+__device__ __forceinline__ uint64_t cut_after_terminator(uint64_t w)
+{
+    const uint64_t M4 = 0x9249249249249248ull, M3 = 0x6DB6DB6DB6DB6DB6ull;
+    const uint64_t zeros = ~(((w & M3) + M3) | w) & M4;
+    if (!zeros) return w;
+    const int lz = __clzll((long long)zeros);
+    return lz ? (w & (~0ull << (64 - lz))) : 0ull;
+}
+
 __device__ __forceinline__ uint32_t sym_code(const uint64_t *__restrict__ T3, uint64_t p)
 {
     const uint64_t bit = 3 * p;

@@ -87,6 +87,9 @@ rs_hist_kernel(const K *__restrict__ keys, uint64_t n, RsPasses P, uint32_t *__r
 // level-0 suffix keys + their digit histograms in one pass over the packed text (see common.cuh).
 // A thread takes FOUR consecutive text positions per step: their windows lie in three consecutive words of the packed
 // text (loaded once), their QL entries are one 8-byte load, and the four keys / positions leave as 16-byte stores.
+// SIX8: the plan is six 8-bit digits (k = 16, the default), so the digits are the key's low six bytes -- cut at compile-time
+// shifts instead of the variable 64-bit shifts and the per-pass branches of the general form.
+template <bool SIX8>
 __global__ void __launch_bounds__(RS_THREADS)
 rs_suffix_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restrict__ QL, uint32_t n, int k, RsPasses P,
                       uint64_t *__restrict__ keys, uint32_t *__restrict__ vals, uint32_t *__restrict__ hist)
@@ -104,6 +107,7 @@ rs_suffix_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restric
         const int s0 = (int)(bit & 63);
         const uint64_t w0 = T3[wi], w1 = T3[wi + 1], w2 = T3[wi + 2];     // (the text is padded: windows past the end read zeros)
         const bool full = vec && p0 + 4 <= n;
+        const int valid = p0 + 4 <= n ? 4 : (int)(n - p0);
         uint32_t ql[4] = {0, 0, 0, 0};
         if (QL) {
             if (full) {
@@ -114,21 +118,28 @@ rs_suffix_keys_kernel(const uint64_t *__restrict__ T3, const uint16_t *__restric
                 for (int i = 0; i < 4; i++) if (p0 + i < n) ql[i] = QL[p0 + i];
             }
         }
+        // the 128 bits that start at the first position's window; the other three windows are cut from them at fixed shifts
+        const uint64_t a0 = s0 ? ((w0 << s0) | (w1 >> (64 - s0))) : w0, a1 = s0 ? ((w1 << s0) | (w2 >> (64 - s0))) : w1;
         uint64_t key[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
-            const int s = s0 + 3 * i;                                        // < 73
-            uint64_t w;
-            if (s < 64) w = s ? ((w0 << s) | (w1 >> (64 - s))) : w0;
-            else { const int t = s - 64; w = t ? ((w1 << t) | (w2 >> (64 - t))) : w1; }
-            w &= ~1ull;
-            const int f = leading_nonzero_fields(w);          // symbols before the first terminator
-            if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
-            const uint64_t kk = w >> (64 - 3 * k);
-            if (p0 + i < n) {
+            uint64_t w = i ? ((a0 << (3 * i)) | (a1 >> (64 - 3 * i))) : a0;
+            w = cut_after_terminator(w & ~1ull);              // symbols after the first terminator do not belong to the suffix
+            const uint64_t kk = SIX8 ? (w >> 16) : (w >> (64 - 3 * k));
+            if (i < valid) {
+                if constexpr (SIX8) {
+                    const uint32_t lo = (uint32_t)kk, hi = (uint32_t)(kk >> 32);
+                    atomicAdd(&sh[copy][0][lo & 255u], 1u);
+                    atomicAdd(&sh[copy][1][(lo >> 8) & 255u], 1u);
+                    atomicAdd(&sh[copy][2][(lo >> 16) & 255u], 1u);
+                    atomicAdd(&sh[copy][3][lo >> 24], 1u);
+                    atomicAdd(&sh[copy][4][hi & 255u], 1u);
+                    atomicAdd(&sh[copy][5][(hi >> 8) & 255u], 1u);
+                } else {
 #pragma unroll
-                for (int q = 0; q < RS_MAX_PASSES; q++)
-                    if (q < P.num) atomicAdd(&sh[copy][q][digit_of(kk, P.shift[q], (1u << P.bits[q]) - 1)], 1u);
+                    for (int q = 0; q < RS_MAX_PASSES; q++)
+                        if (q < P.num) atomicAdd(&sh[copy][q][digit_of(kk, P.shift[q], (1u << P.bits[q]) - 1)], 1u);
+                }
             }
             key[i] = kk | ((uint64_t)ql[i] << 48);            // QL rides in bits the sort ignores (k <= 16); 0 without QL
         }
@@ -706,7 +717,10 @@ int radix_sort_suffix_keys(bfq_ctx *c, const uint64_t *T3, const uint16_t *QL, u
     {
         ProfScope ps(c, PC_KEYS, n * (8 + 4 + 2) + n * 3 / 8);
         int grid = (int)std::min<uint64_t>((uint64_t)c->num_sms * 8, div_up(n, RS_THREADS * 4));
-        rs_suffix_keys_kernel<<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
+        bool six8 = P.num == 6;
+        for (int q = 0; q < P.num; q++) six8 = six8 && P.bits[q] == 8 && P.shift[q] == 8 * q;
+        if (six8) rs_suffix_keys_kernel<true><<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
+        else rs_suffix_keys_kernel<false><<<grid, RS_THREADS, 0, c->stream>>>(T3, QL, (uint32_t)n, k, P, keys_a, pos_a, hist);
         BFQ_CUDA(cudaGetLastError());
     }
     const int flip = radix_passes<uint64_t, uint32_t, RS_ITEMS_MAIN>(c, keys_a, keys_b, pos_a, pos_b, n, P, hist);
