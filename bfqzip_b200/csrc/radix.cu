@@ -501,9 +501,7 @@ __device__ __forceinline__ uint32_t window_top12(uint64_t w)
 }
 __device__ __forceinline__ uint64_t window_key(uint64_t w, int k)
 {
-    const int f = leading_nonzero_fields(w);          // symbols before the first terminator
-    if (f < 21) w &= f ? (~0ull << (64 - 3 * f)) : 0ull;
-    return w >> (64 - 3 * k);
+    return cut_after_terminator(w) >> (64 - 3 * k);
 }
 
 constexpr int RS_TOP_BITS = 12;
