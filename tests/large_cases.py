@@ -15,6 +15,7 @@ from bfqzip_b200 import parallel, synth
 CASES = {
     "cfg2_full": dict(kind="single", nreads=1_000_000, L=100, seed=1001, coverage=40.0, M=2, B=0, egap=True),
     "cfg3_eighth": dict(kind="single", nreads=1_250_000, L=150, seed=1002, coverage=40.0, M=1, B=1),
+    "cfg3_full": dict(kind="single", nreads=10_000_000, L=150, seed=1002, coverage=40.0, M=1, B=1),
     "cfg4_block": dict(kind="paired", npairs=2_500_000, L=150, seed=1003, coverage=5.0, M=3, B=0),
     "cfg5_eighth": dict(kind="single", nreads=6_250_000, L=150, seed=1004, coverage=40.0, M=0, B=0),
 }

@@ -120,6 +120,17 @@ def test_large_device(name, rebuild):
     check(out, st, g, gm, 35)
 
 
+# ---- config 3 in full (10M x 150 bp, M=1 B=1: the largest single-GPU configuration of BASELINE.json), the default part-C path
+def test_cfg3_full_device():
+    import psutil
+    if psutil.virtual_memory().available < 40 << 30:
+        pytest.skip("regenerating 10M x 150 bp on the host takes ~27 GB")
+    (_, _, _), g = case("cfg3_full")
+    out, st, gm = run_dev("cfg3_full", 1, 35)
+    check(out, st, g, gm, 35)
+    _cache.clear()          # 3 GB of host arrays
+
+
 # ---- config 5 (1/8 of the 50M reads, M=0) through the single-collection mode, eight emulated ranks
 def test_cfg5_eighth_single_collection_8_ranks():
     reads, g = case("cfg5_eighth")
