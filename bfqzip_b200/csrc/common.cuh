@@ -109,6 +109,9 @@ __device__ __forceinline__ uint64_t text_window(const uint64_t *__restrict__ T3,
     return r & ~1ull;
 }
 
+// x / 3 for 0 <= x <= 127 (bit counts of a 64-bit word) as one multiply and one shift; the compiler's signed form costs six
+__device__ __forceinline__ uint32_t div3_small(uint32_t x) { return (x * 86u) >> 8; }
+
 // number of leading non-terminator symbols in a window (0..21)
 __device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
 {
@@ -116,8 +119,8 @@ __device__ __forceinline__ int leading_nonzero_fields(uint64_t w)
     const uint64_t M3 = 0x6DB6DB6DB6DB6DB6ull;   // low two bits of each field
     uint64_t t = ((w & M3) + M3) | w;            // field top bit set <=> field != 0
     uint64_t zeros = ~t & M4;
-    int lz = zeros ? __clzll((long long)zeros) : 63;
-    return lz / 3;
+    const int lz = zeros ? __clzll((long long)zeros) : 63;
+    return (int)div3_small((uint32_t)lz);
 }
 
 // the window with every symbol after its first terminator cleared (what `f = leading_nonzero_fields(w); if (f < 21)

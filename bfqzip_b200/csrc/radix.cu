@@ -325,22 +325,38 @@ rs_onesweep_kernel(const K *__restrict__ keys_in, K *__restrict__ keys_out,
 
     // the payload loads are issued here: they are in flight during the chained scan and the key output
     V val[ITEMS];
+    if constexpr (EMIT) {
+        // both bytes are loaded unconditionally (independent loads, all 2 * ITEMS of them in flight); only the rare rows whose
+        // base was replaced (bit 7) touch obase.  Two loops, so that the staged case carries no global-load alternative.
+        if (emit_staged) {                                                   // (a full tile: every loc is valid)
 #pragma unroll
-    for (int i = 0; i < ITEMS; i++) {
-        uint32_t loc = wbase + i * 32;
-        if constexpr (EMIT) {
-            val[i] = (V)0;
-            if (loc < valid) {
-                // both bytes are loaded unconditionally (independent loads, all 2 * ITEMS of them in flight); only the rare
-                // rows whose base was replaced (bit 7) touch obase
-                const uint32_t r = tile_base + loc;
-                const uint8_t q = emit_staged ? s_emit[loc] : __ldcs(src.qflat + r);      // (staged before the first barrier)
-                uint8_t base = emit_staged ? s_emit[TILE + loc] : __ldcs(src.bwt + r);
-                if (q & 0x80) base = src.obase[r];
-                val[i] = (V)(base | ((uint32_t)(q & 0x7F) << 8));
+            for (int i = 0; i < ITEMS; i++) {
+                const uint32_t loc = wbase + i * 32;
+                const uint32_t q = s_emit[loc];                              // (staged before the first barrier)
+                uint32_t base = s_emit[TILE + loc];
+                if (q & 0x80u) base = src.obase[tile_base + loc];
+                val[i] = (V)(base | ((q & 0x7Fu) << 8));
             }
-        } else
+        } else {
+#pragma unroll
+            for (int i = 0; i < ITEMS; i++) {
+                const uint32_t loc = wbase + i * 32;
+                val[i] = (V)0;
+                if (loc < valid) {
+                    const uint32_t r = tile_base + loc;
+                    const uint8_t q = __ldcs(src.qflat + r);
+                    uint8_t base = __ldcs(src.bwt + r);
+                    if (q & 0x80) base = src.obase[r];
+                    val[i] = (V)(base | ((uint32_t)(q & 0x7F) << 8));
+                }
+            }
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; i++) {
+            const uint32_t loc = wbase + i * 32;
             val[i] = (loc < valid) ? vals_in[tile_base + loc] : (V)0;
+        }
     }
 
     // ---- chained scan: exclusive prefix of this digit over all earlier tiles

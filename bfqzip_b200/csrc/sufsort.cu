@@ -227,7 +227,7 @@ __device__ __forceinline__ uint32_t head_lcp(K kprev, K kcur, int ksym)
     // left-align the ksym fields so that field 0 sits in bits 63..61
     const uint64_t a = (uint64_t)kprev << (64 - 3 * ksym), b = (uint64_t)kcur << (64 - 3 * ksym);
     const uint64_t x = a ^ b;
-    const int fm = x ? (__clzll((long long)x) / 3) : ksym;
+    const int fm = x ? (int)div3_small((uint32_t)__clzll((long long)x)) : ksym;
     // symbols before the terminator (fields below ksym are zero padding -> count as terminator)
     const int z = leading_nonzero_fields(b);
     return (uint32_t)min(min(fm, z), ksym);
@@ -262,7 +262,7 @@ __device__ __forceinline__ RefCmp ref_compare(const uint64_t *__restrict__ T3, c
             const uint64_t wm = text_window(T3, pm + 21u * j), wr = text_window(T3, pr + 21u * j);
             const uint64_t x = wm ^ wr;
             if (x) {
-                const uint32_t f = (uint32_t)(__clzll((long long)x) / 3);
+                const uint32_t f = div3_small((uint32_t)__clzll((long long)x));
                 if (21u * j + f < lm) {                   // both symbols at the difference come from the two windows
                     o.l = 21u * j + f;
                     o.c = (uint32_t)((wm << (3u * f)) >> 61);
@@ -295,7 +295,7 @@ __device__ __forceinline__ RefCmp v_compare(const uint64_t *__restrict__ T3, con
         const uint64_t wm = text_window(T3, pm + 21u * j), wr = s_v[j];
         const uint64_t x = wm ^ wr;
         if (x) {
-            const uint32_t f = (uint32_t)(__clzll((long long)x) / 3);
+            const uint32_t f = div3_small((uint32_t)__clzll((long long)x));
             if (21u * j + f < lm) {
                 o.l = 21u * j + f;
                 o.c = (uint32_t)((wm << (3u * f)) >> 61);
